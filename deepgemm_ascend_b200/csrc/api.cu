@@ -1,0 +1,596 @@
+// C ABI of the B200 dynamic-shape matmul (see include/dga_b200.h) and the
+// launch glue: TMA tensor-map encoding, plan -> kernel-instance dispatch.
+// Role of op_kernel/catlass_dynamic_matmul.h:32-60 (variant dispatch) and of
+// op_host/catlass_dynamic_matmul_tiling.cpp:40-122 (tiling -> launch record).
+// There is deliberately no CPU fallback: without a CUDA driver every compute
+// entry point fails with ACLNN_ERR_RUNTIME_ERROR.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cudaTypedefs.h>
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+
+#include "gemm_smallm_sm100.cuh"
+#include "tile_selector.h"
+
+namespace dga {
+
+static std::atomic<uint64_t> g_launches{0};
+
+#define DGA_CUDA(expr)                                                                       \
+    do {                                                                                     \
+        cudaError_t e__ = (expr);                                                            \
+        if (e__ != cudaSuccess) {                                                            \
+            set_error(std::string(#expr) + " failed: " + cudaGetErrorString(e__));           \
+            return ACLNN_ERR_RUNTIME_ERROR;                                                  \
+        }                                                                                    \
+    } while (0)
+
+// ---- TMA descriptors --------------------------------------------------------------------------------
+static PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+    });
+    return fn;
+}
+
+static CUtensorMapDataType tmap_dtype(int32_t dtype) {
+    switch (dtype) {
+        case ACL_FLOAT: return CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+        case ACL_FLOAT16: return CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+        case ACL_BF16: return CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+        default: return CU_TENSOR_MAP_DATA_TYPE_UINT8;
+    }
+}
+
+// 2-D row-major tensor [outer, inner] with leading dimension ld (elements); box = [box_outer, box_inner].
+static int make_tmap_2d(CUtensorMap* map, const void* ptr, int32_t dtype, uint64_t inner, uint64_t outer, uint64_t ld,
+                        uint32_t box_inner, uint32_t box_outer, CUtensorMapSwizzle swizzle,
+                        CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B) {
+    auto fn = encode_fn();
+    if (fn == nullptr) {
+        set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver)");
+        return ACLNN_ERR_RUNTIME_ERROR;
+    }
+    const uint32_t eb = elem_bytes(dtype);
+    cuuint64_t dims[2] = {inner, outer};
+    cuuint64_t strides[1] = {ld * eb};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || (strides[0] & 15) != 0) {
+        set_error("TMA needs 16-byte aligned base pointers and leading dimensions");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    CUresult r = fn(map, tmap_dtype(dtype), 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string(int(r)));
+        return ACLNN_ERR_RUNTIME_ERROR;
+    }
+    return ACLNN_SUCCESS;
+}
+
+// ---- launch records ---------------------------------------------------------------------------------
+struct DenseLaunch {
+    DgaTilingPlan plan;
+    const void* a;
+    const void* b;
+    void* d;
+    uint64_t lda, ldb, ldd;  // elements
+    CUtensorMap tm_a, tm_b, tm_d;
+    bool encoded = false;
+};
+
+template <typename K>
+static int set_smem_attr(K kernel, uint32_t bytes) {
+    DGA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
+    return ACLNN_SUCCESS;
+}
+
+template <int kCta, typename OutT, bool kBMn>
+static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaStream_t stream) {
+    auto kernel = gemm_sm100_kernel<kCta, OutT, kBMn>;
+    int rc = set_smem_attr(kernel, L.plan.smemBytes);
+    if (rc != ACLNN_SUCCESS) return rc;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(L.plan.blockDim);
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.dynamicSmemBytes = L.plan.smemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kCta;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, gp));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return ACLNN_SUCCESS;
+}
+
+template <int kCta, bool kBMn>
+static int launch_common_out(const DenseLaunch& L, const GemmParams& gp, cudaStream_t stream) {
+    switch (L.plan.outDtype) {
+        case ACL_BF16: return launch_common_inst<kCta, __nv_bfloat16, kBMn>(L, gp, stream);
+        case ACL_FLOAT16: return launch_common_inst<kCta, __half, kBMn>(L, gp, stream);
+        case ACL_FLOAT: return launch_common_inst<kCta, float, kBMn>(L, gp, stream);
+    }
+    set_error("unsupported output dtype");
+    return ACLNN_ERR_PARAM_INVALID;
+}
+
+static int encode_common(DenseLaunch& L) {
+    const DgaTilingPlan& p = L.plan;
+    const uint32_t cta = p.ctaGroup, load_n = p.n1 / cta;
+    int rc = make_tmap_2d(&L.tm_a, L.a, p.dtype, p.k, p.m, L.lda, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc != ACLNN_SUCCESS) return rc;
+    if (p.layoutTagB == 1)  // weight stored [N, K]
+        rc = make_tmap_2d(&L.tm_b, L.b, p.dtype, p.k, p.n, L.ldb, 64, load_n, CU_TENSOR_MAP_SWIZZLE_128B);
+    else  // row-major [K, N]: boxes of 64 columns x 64 k-rows
+        rc = make_tmap_2d(&L.tm_b, L.b, p.dtype, p.n, p.k, L.ldb, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc != ACLNN_SUCCESS) return rc;
+    const bool wide = elem_bytes(p.outDtype) == 4;
+    return make_tmap_2d(&L.tm_d, L.d, p.outDtype, p.n, p.m, L.ldd, 32, 128,
+                        wide ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B);
+}
+
+static int launch_common(DenseLaunch& L, cudaStream_t stream) {
+    const DgaTilingPlan& p = L.plan;
+    if (!L.encoded) {
+        int rc = encode_common(L);
+        if (rc != ACLNN_SUCCESS) return rc;
+        L.encoded = true;
+    }
+    const uint32_t cta = p.ctaGroup;
+    GemmParams gp{};
+    gp.m = p.m; gp.n = p.n; gp.k = p.k;
+    gp.block_n = p.n1;
+    gp.num_stages = p.stages;
+    gp.k_blocks = ceil_div(p.k, 64);
+    gp.num_m_blocks = ceil_div(p.m, 128 * cta);
+    gp.num_n_blocks = ceil_div(p.n, p.n1);
+    gp.raster_group = p.swizzleOffset;
+    gp.raster_along_m = p.swizzleDirection;
+    gp.idesc = make_idesc(128 * cta, p.n1, p.dtype == ACL_BF16 ? 1u : 0u, 0, p.layoutTagB == 1 ? 0u : 1u);
+    gp.b_stage_bytes = (p.n1 / cta) * 128;
+    if (cta == 2)
+        return p.layoutTagB == 1 ? launch_common_out<2, false>(L, gp, stream) : launch_common_out<2, true>(L, gp, stream);
+    return p.layoutTagB == 1 ? launch_common_out<1, false>(L, gp, stream) : launch_common_out<1, true>(L, gp, stream);
+}
+
+// ---- small-M swap-AB split-K ---------------------------------------------------------------------------
+template <typename OutT>
+static int launch_splitk_inst(const DenseLaunch& L, const SmallMParams& sp, cudaStream_t stream) {
+    auto kernel = gemm_smallm_sm100_kernel<OutT>;
+    int rc = set_smem_attr(kernel, L.plan.smemBytes);
+    if (rc != ACLNN_SUCCESS) return rc;
+    if (sp.split > 8) DGA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(L.plan.blockDim);
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.dynamicSmemBytes = L.plan.smemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = sp.split;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, sp));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return ACLNN_SUCCESS;
+}
+
+static int launch_splitk(DenseLaunch& L, cudaStream_t stream) {
+    const DgaTilingPlan& p = L.plan;
+    const uint32_t m_pad = p.m1;
+    if (!L.encoded) {
+        // tm_a slot holds the weight map (UMMA A operand), tm_b the activation map (UMMA B operand)
+        int rc = make_tmap_2d(&L.tm_a, L.b, p.dtype, p.k, p.n, L.ldb, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc != ACLNN_SUCCESS) return rc;
+        rc = make_tmap_2d(&L.tm_b, L.a, p.dtype, p.k, p.m, L.lda, 64, m_pad, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc != ACLNN_SUCCESS) return rc;
+        L.encoded = true;
+    }
+    SmallMParams sp{};
+    sp.m = p.m; sp.n = p.n; sp.k = p.k;
+    sp.m_pad = m_pad;
+    sp.split = p.splitkFactor;
+    sp.num_stages = p.stages;
+    sp.k_blocks = ceil_div(p.k, 64);
+    sp.ldc = static_cast<uint32_t>(L.ldd);
+    sp.idesc = make_idesc(128, m_pad, p.dtype == ACL_BF16 ? 1u : 0u, 0, 0);
+    uint32_t cols = 32;
+    while (cols < m_pad) cols <<= 1;
+    sp.tmem_cols = cols;
+    sp.out = L.d;
+    if (sp.k_blocks < sp.split || uint64_t(p.stages) * (16384 + m_pad * 128) < uint64_t(m_pad) * 512) {
+        set_error("split-K plan infeasible for this shape");
+        return ACLNN_ERR_INNER_TILING_ERROR;
+    }
+    switch (p.outDtype) {
+        case ACL_BF16: return launch_splitk_inst<__nv_bfloat16>(L, sp, stream);
+        case ACL_FLOAT16: return launch_splitk_inst<__half>(L, sp, stream);
+        case ACL_FLOAT: return launch_splitk_inst<float>(L, sp, stream);
+    }
+    set_error("unsupported output dtype");
+    return ACLNN_ERR_PARAM_INVALID;
+}
+
+static int launch_dense(DenseLaunch& L, cudaStream_t stream) {
+    switch (L.plan.kernelSerial) {
+        case DGA_KERNEL_COMMON:
+        case DGA_KERNEL_SMALL: return launch_common(L, stream);
+        case DGA_KERNEL_SPLITK: return launch_splitk(L, stream);
+    }
+    set_error("kernel variant " + std::to_string(int(L.plan.kernelSerial)) + " is not built");
+    return ACLNN_ERR_INNER_TILING_ERROR;
+}
+
+__global__ void mmad_custom_stub(const void*, const void*, void*) {}
+
+}  // namespace dga
+
+// =========================================================================================== C ABI ====
+using namespace dga;
+
+struct aclOpExecutor {
+    DenseLaunch dense;
+    bool repeatable = false;
+};
+
+extern "C" {
+
+aclTensor* aclCreateTensor(const int64_t* viewDims, uint64_t viewDimsNum, aclDataType dataType, const int64_t* stride,
+                           int64_t offset, aclFormat, const int64_t*, uint64_t, void* tensorData) {
+    if (viewDims == nullptr || viewDimsNum > 8) return nullptr;
+    aclTensor* t = new aclTensor{};
+    t->dtype = dataType;
+    t->ndim = static_cast<int32_t>(viewDimsNum);
+    int64_t run = 1;
+    for (int64_t i = int64_t(viewDimsNum) - 1; i >= 0; --i) {
+        t->shape[i] = viewDims[i];
+        t->stride[i] = stride ? stride[i] : run;
+        run *= viewDims[i];
+    }
+    t->data = static_cast<char*>(tensorData) + offset * int64_t(elem_bytes(dataType));
+    return t;
+}
+
+aclnnStatus aclDestroyTensor(const aclTensor* tensor) {
+    delete tensor;
+    return ACLNN_SUCCESS;
+}
+
+static bool dtype_ok_in(int32_t d) { return d == ACL_FLOAT16 || d == ACL_BF16; }
+
+// Shared by phase 1 and dgaMatmulWithPlan: InferShape / InferDataType / TilingFunc checks + layout detection.
+static aclnnStatus validate_dense(const aclTensor* self, const aclTensor* mat2, const aclTensor* out, DenseLaunch& L) {
+    if (self == nullptr || mat2 == nullptr || out == nullptr) {
+        set_error("null tensor");
+        return ACLNN_ERR_PARAM_NULLPTR;
+    }
+    if (self->ndim != 2 || mat2->ndim != 2 || out->ndim != 2) {  // catlass_dynamic_matmul.cpp:22-26
+        set_error("Invalid input dimensions. self, mat2 and out must be 2-D");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (self->dtype != mat2->dtype || !dtype_ok_in(self->dtype)) {  // catlass_dynamic_matmul.cpp:37-46
+        set_error("self and mat2 must share a dtype in {float16, bfloat16}");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (out->dtype != self->dtype && out->dtype != ACL_FLOAT) {
+        set_error("out dtype must equal the input dtype (or float32 for the framework path)");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    const int64_t m = self->shape[0], ka = self->shape[1], kb = mat2->shape[0], n = mat2->shape[1];
+    if (ka != kb) {  // catlass_dynamic_matmul_tiling.cpp:96-100
+        set_error("K dimension mismatch: self[1]=" + std::to_string(ka) + " mat2[0]=" + std::to_string(kb));
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (out->shape[0] != m || out->shape[1] != n) {
+        set_error("out shape must be [self.dim0, mat2.dim1]");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (m <= 0 || n <= 0 || ka <= 0 || m > UINT32_MAX || n > UINT32_MAX || ka > UINT32_MAX) {
+        set_error("m, n, k must be positive 32-bit extents");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (self->stride[1] != 1 && !(ka == 1)) {
+        set_error("self must be row-major (unit stride along K)");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (out->stride[1] != 1 && !(n == 1)) {
+        set_error("out must be row-major");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    DgaTilingPlan& p = L.plan;
+    p = DgaTilingPlan{};
+    p.m = uint32_t(m); p.n = uint32_t(n); p.k = uint32_t(ka);
+    p.dtype = uint8_t(self->dtype);
+    p.outDtype = uint8_t(out->dtype);
+    // the reference's "todo use mat stride to check transpose" (catlass_dynamic_matmul_tiling.cpp:82-84)
+    if (mat2->stride[0] == 1 && (mat2->stride[1] >= ka || n == 1)) {
+        p.layoutTagB = 1;
+        L.ldb = n == 1 ? uint64_t(ka) : uint64_t(mat2->stride[1]);
+    } else if (mat2->stride[1] == 1 && mat2->stride[0] >= n) {
+        p.layoutTagB = 0;
+        L.ldb = uint64_t(mat2->stride[0]);
+    } else {
+        set_error("mat2 must be column-major (weight stored [N,K]) or row-major [K,N]");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    L.lda = m == 1 ? uint64_t(ka) : uint64_t(self->stride[0]);
+    L.ldd = m == 1 ? uint64_t(n) : uint64_t(out->stride[0]);
+    if (L.lda < uint64_t(ka) || L.ldd < uint64_t(n)) {
+        set_error("leading dimension smaller than the row length");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    L.a = self->data; L.b = mat2->data; L.d = out->data;
+    return ACLNN_SUCCESS;
+}
+
+static aclnnStatus check_strides(const DenseLaunch& L) {
+    const uint32_t ib = elem_bytes(L.plan.dtype), ob = elem_bytes(L.plan.outDtype);
+    if ((L.lda * ib) % 16 || (L.ldb * ib) % 16 || (L.ldd * ob) % 16) {
+        set_error("leading dimensions must be 16-byte aligned (stride repack not built yet)");
+        return ACLNN_ERR_INNER_TILING_ERROR;
+    }
+    return ACLNN_SUCCESS;
+}
+
+aclnnStatus aclnnCatlassDynamicMatmulGetWorkspaceSize(const aclTensor* self, const aclTensor* mat2,
+                                                      const aclTensor* out, uint64_t* workspaceSize,
+                                                      aclOpExecutor** executor) {
+    if (workspaceSize == nullptr || executor == nullptr) {
+        set_error("null output argument");
+        return ACLNN_ERR_PARAM_NULLPTR;
+    }
+    aclOpExecutor* ex = new aclOpExecutor{};
+    aclnnStatus rc = validate_dense(self, mat2, out, ex->dense);
+    if (rc == ACLNN_SUCCESS) rc = select_kernel_with_cache(ex->dense.plan);
+    if (rc == ACLNN_SUCCESS) rc = check_strides(ex->dense);
+    if (rc != ACLNN_SUCCESS) {
+        delete ex;
+        return rc;
+    }
+    *workspaceSize = ex->dense.plan.workspaceBytes;
+    *executor = ex;
+    return ACLNN_SUCCESS;
+}
+
+aclnnStatus aclnnCatlassDynamicMatmul(void* workspace, uint64_t workspaceSize, aclOpExecutor* executor,
+                                      aclrtStream stream) {
+    if (executor == nullptr) {
+        set_error("null executor");
+        return ACLNN_ERR_PARAM_NULLPTR;
+    }
+    aclnnStatus rc = ACLNN_SUCCESS;
+    if (workspaceSize < executor->dense.plan.workspaceBytes ||
+        (executor->dense.plan.workspaceBytes > 0 && workspace == nullptr)) {
+        set_error("workspace too small");
+        rc = ACLNN_ERR_PARAM_INVALID;
+    } else {
+        rc = launch_dense(executor->dense, static_cast<cudaStream_t>(stream));
+    }
+    if (!executor->repeatable) delete executor;
+    return rc;
+}
+
+aclnnStatus dgaSetExecutorRepeatable(aclOpExecutor* executor) {
+    if (executor == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    executor->repeatable = true;
+    return ACLNN_SUCCESS;
+}
+aclnnStatus dgaDestroyExecutor(aclOpExecutor* executor) {
+    delete executor;
+    return ACLNN_SUCCESS;
+}
+
+aclnnStatus dgaMatmulWithPlan(const aclTensor* self, const aclTensor* mat2, const aclTensor* out,
+                              const DgaTilingPlan* plan, void*, uint64_t, aclrtStream stream) {
+    if (plan == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    DenseLaunch L;
+    aclnnStatus rc = validate_dense(self, mat2, out, L);
+    if (rc != ACLNN_SUCCESS) return rc;
+    DgaTilingPlan p = *plan;
+    // shape, dtype and layout always come from the tensors
+    p.m = L.plan.m; p.n = L.plan.n; p.k = L.plan.k;
+    p.dtype = L.plan.dtype; p.outDtype = L.plan.outDtype; p.layoutTagB = L.plan.layoutTagB;
+    rc = finalize_plan(p);
+    if (rc != ACLNN_SUCCESS) return rc;
+    L.plan = p;
+    rc = check_strides(L);
+    if (rc != ACLNN_SUCCESS) return rc;
+    return launch_dense(L, static_cast<cudaStream_t>(stream));
+}
+
+// ---- fp8 block-scaled (filled in by gemm_fp8_sm100.cuh) ------------------------------------------------
+aclnnStatus dgaFp8BlockScaledMatmulGetWorkspaceSize(const aclTensor*, const aclTensor*, const aclTensor*,
+                                                    const aclTensor*, const aclTensor*, uint64_t*, aclOpExecutor**) {
+    set_error("fp8 block-scaled kernel is not built yet");
+    return ACLNN_ERR_INNER_TILING_ERROR;
+}
+aclnnStatus dgaFp8BlockScaledMatmul(void*, uint64_t, aclOpExecutor*, aclrtStream) {
+    set_error("fp8 block-scaled kernel is not built yet");
+    return ACLNN_ERR_INNER_TILING_ERROR;
+}
+
+// ---- host tiling -------------------------------------------------------------------------------------
+static void seed_plan(DgaTilingPlan& p, uint32_t m, uint32_t n, uint32_t k, int32_t dtype, int32_t outDtype,
+                      int32_t layoutTagB) {
+    p = DgaTilingPlan{};
+    p.m = m; p.n = n; p.k = k;
+    p.dtype = uint8_t(dtype); p.outDtype = uint8_t(outDtype); p.layoutTagB = uint8_t(layoutTagB);
+}
+aclnnStatus dgaSelectKernel(uint32_t m, uint32_t n, uint32_t k, int32_t dtype, int32_t outDtype, int32_t layoutTagB,
+                            DgaTilingPlan* plan) {
+    if (plan == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    seed_plan(*plan, m, n, k, dtype, outDtype, layoutTagB);
+    return select_kernel(*plan);
+}
+aclnnStatus dgaSelectKernelWithCache(uint32_t m, uint32_t n, uint32_t k, int32_t dtype, int32_t outDtype,
+                                     int32_t layoutTagB, DgaTilingPlan* plan) {
+    if (plan == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    seed_plan(*plan, m, n, k, dtype, outDtype, layoutTagB);
+    return select_kernel_with_cache(*plan);
+}
+aclnnStatus dgaTilingCacheSet(const DgaTilingPlan* plan) {
+    if (plan == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    DgaTilingPlan p = *plan;
+    aclnnStatus rc = finalize_plan(p);
+    return rc != ACLNN_SUCCESS ? rc : cache_set(p);
+}
+aclnnStatus dgaTilingCacheGet(uint32_t m, uint32_t n, uint32_t k, int32_t dtype, int32_t outDtype, int32_t layoutTagB,
+                              DgaTilingPlan* plan) {
+    if (plan == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    seed_plan(*plan, m, n, k, dtype, outDtype, layoutTagB);
+    return cache_get(*plan);
+}
+aclnnStatus dgaTilingCacheClear(void) { cache_clear(); return ACLNN_SUCCESS; }
+uint64_t dgaTilingCacheSize(void) { return cache_size(); }
+aclnnStatus dgaTilingCacheLoadCsv(const char* path) { return cache_load_csv(path); }
+aclnnStatus dgaTilingCacheSaveCsv(const char* path) { return cache_save_csv(path); }
+
+aclnnStatus dgaGetPlatformInfo(DgaPlatformInfo* info) {
+    if (info == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    const PlatformInfo& hw = platform();
+    *info = DgaPlatformInfo{hw.smCount, hw.smemBytes, hw.tmemCols, hw.l2Bytes, hw.hbmGBs, hw.denseTflops16, hw.denseTflops8};
+    return ACLNN_SUCCESS;
+}
+aclnnStatus dgaSetPlatformInfo(const DgaPlatformInfo* info) {
+    if (info == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    if (info->smCount < 2 || info->smemBytes < 65536) {
+        set_error("implausible platform info");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    PlatformInfo& hw = platform();
+    hw.smCount = info->smCount; hw.smemBytes = info->smemBytes; hw.tmemCols = info->tmemCols;
+    hw.l2Bytes = info->l2Bytes; hw.hbmGBs = info->hbmGBs; hw.denseTflops16 = info->denseTflops16;
+    hw.denseTflops8 = info->denseTflops8;
+    return ACLNN_SUCCESS;
+}
+
+// ---- framework entry points ------------------------------------------------------------------------------
+aclnnStatus dgaRunMmadCustom(const void* x, const void* y, void* z, aclrtStream stream) {
+    mmad_custom_stub<<<8, 32, 0, static_cast<cudaStream_t>(stream)>>>(x, y, z);  // blockDim 8: gemm.hpp:18
+    DGA_CUDA(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return ACLNN_SUCCESS;
+}
+
+// z[m,n] fp32 = x[m,k] * y[k,n], both row-major contiguous 16-bit.
+static aclnnStatus framework_gemm(const void* x, const void* y, void* z, uint32_t m, uint32_t n, uint32_t k,
+                                  int32_t dtype, cudaStream_t stream) {
+    DenseLaunch L;
+    seed_plan(L.plan, m, n, k, dtype, ACL_FLOAT, /*layoutTagB=*/0);
+    aclnnStatus rc = select_kernel_with_cache(L.plan);
+    if (rc != ACLNN_SUCCESS) return rc;
+    L.a = x; L.b = y; L.d = z;
+    L.lda = k; L.ldb = n; L.ldd = n;
+    return launch_dense(L, stream);
+}
+
+aclnnStatus dgaRunMmadRtc(const void* x, const void* y, void* z, uint32_t batch, uint32_t m, uint32_t n, uint32_t k,
+                          aclrtStream stream) {
+    if (x == nullptr || y == nullptr || z == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    for (uint32_t b = 0; b < batch; ++b) {  // batch loop of the reference kernel: generate_code.hpp:149-153
+        const char* xb = static_cast<const char*>(x) + uint64_t(b) * m * k * 2;
+        const char* yb = static_cast<const char*>(y) + uint64_t(b) * k * n * 2;
+        char* zb = static_cast<char*>(z) + uint64_t(b) * m * n * 4;
+        aclnnStatus rc = framework_gemm(xb, yb, zb, m, n, k, ACL_BF16, s);
+        if (rc != ACLNN_SUCCESS) return rc;
+    }
+    DGA_CUDA(cudaStreamSynchronize(s));  // the reference blocks here (gemm.hpp:110)
+    return ACLNN_SUCCESS;
+}
+
+static uint32_t align16(uint32_t x) { return (x + 15u) & ~15u; }
+
+aclnnStatus dgaGetBenchConfig(uint32_t m, uint32_t n, uint32_t k, int32_t* params) {
+    if (params == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    for (int i = 0; i < 6; ++i) {
+        if (params[i] <= 0) {
+            set_error("bench knobs params[0..5] must be positive");
+            return ACLNN_ERR_PARAM_INVALID;
+        }
+    }
+    // Loop bounds of the reference's 16x16-block MMAD kernel for the caller's six knobs
+    // (jit/get_best_config.hpp:93-153); order of the 22 outputs as in gemm_bench.hpp:66-69.
+    const uint32_t m_sections = params[0], n_sections = params[1], m_sec = params[2], n_sec = params[3];
+    const uint32_t k_iter = params[4], db = params[5];
+    const uint32_t mb = align16(m) / 16, nb = align16(n) / 16, kb = align16(k) / 16;
+    const uint32_t db_num = k_iter / db;
+    uint32_t r_mb = mb % m_sec, r_nb = nb % n_sec;
+    if (r_mb == 0) r_mb = m_sec;
+    if (r_nb == 0) r_nb = n_sec;
+    const uint32_t k_iters = (kb + k_iter - 1) / k_iter;
+    const uint32_t k_tail = kb % k_iter;
+    uint32_t r_db_num, r_kb;
+    if (k_tail == 0) {
+        r_db_num = db_num;
+        r_kb = db;
+    } else {
+        r_db_num = (k_tail + db - 1) / db;
+        r_kb = k_tail - (r_db_num - 1) * db;
+    }
+    const uint32_t m_iters = (mb + m_sec - 1) / m_sec, n_iters = (nb + n_sec - 1) / n_sec;
+    const uint32_t m_parts = m_iters / m_sections, n_parts = n_iters / n_sections;
+    const uint32_t out[22] = {m, n, k, 1u, k_iters, mb, nb, kb, m_parts * m_sec, n_parts * n_sec,
+                              align16(m) - m, align16(n) - n, align16(k) - k, db_num, m_parts, n_parts,
+                              m_iters - (m_sections - 1) * m_parts, n_iters - (n_sections - 1) * n_parts,
+                              r_mb, r_nb, r_kb, r_db_num};
+    for (int i = 0; i < 22; ++i) params[6 + i] = static_cast<int32_t>(out[i]);
+    return ACLNN_SUCCESS;
+}
+
+aclnnStatus dgaRunMmadBench(const void* x, const void* y, void* z, uint32_t m, uint32_t n, uint32_t k, int32_t* params,
+                            aclrtStream stream) {
+    if (x == nullptr || y == nullptr || z == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    aclnnStatus rc = dgaGetBenchConfig(m, n, k, params);
+    if (rc != ACLNN_SUCCESS) return rc;
+    // The six knobs tile an Ascend cube core (16x16 blocks in L1/L0); they are advisory on B200, where the
+    // tile comes from the selector / plan cache.
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    rc = framework_gemm(x, y, z, m, n, k, ACL_FLOAT16, s);
+    if (rc != ACLNN_SUCCESS) return rc;
+    DGA_CUDA(cudaStreamSynchronize(s));  // gemm_bench.hpp:112
+    return ACLNN_SUCCESS;
+}
+
+// ---- N-sharding ------------------------------------------------------------------------------------------
+aclnnStatus dgaNShardRange(uint32_t n, uint32_t worldSize, uint32_t rank, uint32_t* nBegin, uint32_t* nCount) {
+    if (nBegin == nullptr || nCount == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    if (worldSize == 0 || rank >= worldSize) {
+        set_error("rank out of range");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    // contiguous slices in units of 256 columns (one CTA-pair tile) so no rank gets a ragged interior tile
+    const uint32_t units = ceil_div(n, 256);
+    const uint32_t base = units / worldSize, extra = units % worldSize;
+    const uint32_t u0 = rank * base + std::min(rank, extra);
+    const uint32_t u1 = u0 + base + (rank < extra ? 1u : 0u);
+    const uint32_t b = std::min(n, u0 * 256), e = std::min(n, u1 * 256);
+    *nBegin = b;
+    *nCount = e - b;
+    return ACLNN_SUCCESS;
+}
+
+// ---- misc --------------------------------------------------------------------------------------------------
+const char* dgaGetLastError(void) { return last_error(); }
+uint64_t dgaKernelLaunchCount(void) { return g_launches.load(); }
+const char* dgaVersion(void) { return "dga-b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

@@ -1,0 +1,323 @@
+// Persistent, warp-specialised dense GEMM for sm_100a:  D[M,N] = A[M,K] * B[N,K]^T
+//
+// Replaces the reference's CommonMatmulKernel / SmallMatmulKernel device path
+// (aclnn_catlass_dynamic_matmul/op_kernel/kernel/common_matmul_kernel.h:28-78,
+// small_matmul_kernel.h:28-74) and, with kBMn = true and OutT = float, the
+// framework's row-major x row-major fp32-output MMAD kernel
+// (deep_gemm_ascend/framework/csrc/jit/generate_code.hpp:123-369).
+//
+// Shape of the machine:
+//   warp 0 lane 0 : TMA producer   (global -> smem ring, SWIZZLE_128B boxes)
+//   warp 1 lane 0 : MMA issuer     (tcgen05.mma, fp32 accumulators in TMEM; leader CTA only)
+//   warp 2        : TMEM allocator / deallocator
+//   warps 4..7    : epilogue       (tcgen05.ld -> cvt -> swizzled smem -> TMA store)
+// kCta = 2 pairs two CTAs (one cluster) on a 256 x BLOCK_N tile with
+// cta_group::2 MMAs: each CTA loads its own 128 rows of A and half of the
+// B rows, so per-SM smem traffic for B is halved.
+// Two TMEM accumulator stages let the epilogue of tile i overlap the mainloop
+// of tile i+1.  BLOCK_N, stage count and rasterisation are runtime values
+// chosen by the host tile selector (tile_selector.cpp).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cstdint>
+
+#include "ptx.cuh"
+
+namespace dga {
+
+constexpr uint32_t kBlockM = 128;      // rows per CTA (UMMA M = 128 * kCta)
+constexpr uint32_t kBlockKBytes = 128; // one SWIZZLE_128B atom along K per stage
+constexpr uint32_t kEpiCols = 32;      // columns per epilogue chunk / TMA store box
+constexpr uint32_t kNumThreads = 256;
+constexpr uint32_t kMaxStages = 12;
+
+struct GemmParams {
+    uint32_t m, n, k;
+    uint32_t block_n;        // cluster-tile N (multiple of 16 * kCta, <= 256)
+    uint32_t num_stages;     // smem ring depth
+    uint32_t k_blocks;       // ceil(k / elements-per-128B)
+    uint32_t num_m_blocks;   // cluster tiles along M
+    uint32_t num_n_blocks;   // cluster tiles along N
+    uint32_t raster_group;   // tiles per rasterisation group (role of swizzleOffset)
+    uint32_t raster_along_m; // 1: consecutive tiles walk M inside a group of N blocks (role of swizzleDirection)
+    uint32_t idesc;          // tcgen05 instruction descriptor
+    uint32_t b_stage_bytes;  // bytes of B per CTA per stage
+};
+
+// --- descriptors -----------------------------------------------------------
+// tcgen05 shared-memory matrix descriptor (sm_100 layout): start>>4 [0,14),
+// LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout type [61,64).
+__host__ __device__ constexpr uint64_t make_smem_desc_hi(uint32_t sbo_bytes, uint32_t layout_type) {
+    return (static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46) |
+           (static_cast<uint64_t>(layout_type) << 61);
+}
+constexpr uint32_t kLayoutSw128 = 2;
+
+// Instruction descriptor for kind::f16 / kind::f8f6f4 with fp32 accumulation.
+// a_fmt/b_fmt: f16 kind: 0 = fp16, 1 = bf16;  f8f6f4 kind: 0 = e4m3, 1 = e5m2.
+__host__ __device__ constexpr uint32_t make_idesc(uint32_t umma_m, uint32_t umma_n, uint32_t ab_fmt,
+                                                  uint32_t a_mn_major, uint32_t b_mn_major) {
+    return (1u << 4) | (ab_fmt << 7) | (ab_fmt << 10) | (a_mn_major << 15) | (b_mn_major << 16) |
+           ((umma_n >> 3) << 17) | ((umma_m >> 4) << 24);
+}
+
+// --- tile order --------------------------------------------------------------
+// Grouped rasterisation: tiles are walked in groups of `raster_group` blocks of
+// one dimension so that the ~74 tiles in flight cover a compact rectangle and
+// share A/B panels in L2 (what DynamicGemmIdentityBlockSwizzle(offset,
+// direction) does for the reference, tiling_params.h:63-64).
+__device__ __forceinline__ void tile_coords(const GemmParams& p, uint32_t t, uint32_t& mb, uint32_t& nb) {
+    const uint32_t g = p.raster_group;
+    if (p.raster_along_m) {
+        // groups of g N-blocks; inside a group walk N fastest, then M
+        const uint32_t per_group = g * p.num_m_blocks;
+        const uint32_t gi = t / per_group, r = t - gi * per_group;
+        const uint32_t first = gi * g;
+        const uint32_t size = min(g, p.num_n_blocks - first);
+        mb = r / size;
+        nb = first + (r - mb * size);
+    } else {
+        const uint32_t per_group = g * p.num_n_blocks;
+        const uint32_t gi = t / per_group, r = t - gi * per_group;
+        const uint32_t first = gi * g;
+        const uint32_t size = min(g, p.num_m_blocks - first);
+        nb = r / size;
+        mb = first + (r - nb * size);
+    }
+}
+
+template <typename OutT> struct OutPack;
+template <> struct OutPack<__nv_bfloat16> {
+    static __device__ __forceinline__ uint32_t pack(float a, float b) {
+        __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<uint32_t*>(&v);
+    }
+};
+template <> struct OutPack<__half> {
+    static __device__ __forceinline__ uint32_t pack(float a, float b) {
+        __half2 v = __floats2half2_rn(a, b);
+        return *reinterpret_cast<uint32_t*>(&v);
+    }
+};
+
+// Write this thread's 32 fp32 accumulator columns as one row of the staging
+// tile, in the swizzle the TMA store descriptor expects (SWIZZLE_64B for
+// 2-byte outputs: 64 B rows; SWIZZLE_128B for fp32: 128 B rows).
+template <typename OutT>
+__device__ __forceinline__ void stage_row(uint32_t stage_base, uint32_t row, const uint32_t (&v)[32]) {
+    if constexpr (sizeof(OutT) == 2) {
+        const uint32_t row_base = stage_base + row * 64;
+        const uint32_t x = (row >> 1) & 3;
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j) {
+            const uint32_t a = OutPack<OutT>::pack(__uint_as_float(v[8 * j + 0]), __uint_as_float(v[8 * j + 1]));
+            const uint32_t b = OutPack<OutT>::pack(__uint_as_float(v[8 * j + 2]), __uint_as_float(v[8 * j + 3]));
+            const uint32_t c = OutPack<OutT>::pack(__uint_as_float(v[8 * j + 4]), __uint_as_float(v[8 * j + 5]));
+            const uint32_t d = OutPack<OutT>::pack(__uint_as_float(v[8 * j + 6]), __uint_as_float(v[8 * j + 7]));
+            ptx::st_shared_v4(row_base + ((j ^ x) << 4), a, b, c, d);
+        }
+    } else {
+        const uint32_t row_base = stage_base + row * 128;
+        const uint32_t x = row & 7;
+#pragma unroll
+        for (uint32_t j = 0; j < 8; ++j)
+            ptx::st_shared_v4(row_base + ((j ^ x) << 4), v[4 * j + 0], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+}
+
+// Shared-memory carve-up (offsets from a 1024-aligned base; identical in both
+// CTAs of a pair, which cta_group::2 descriptors rely on).
+struct SmemLayout {
+    uint32_t d_stage_bytes, a_stage_bytes, b_stage_bytes;
+    uint32_t off_d, off_a, off_b, off_bar, total;
+};
+__host__ __device__ inline SmemLayout make_smem_layout(uint32_t out_elem_bytes, uint32_t b_stage_bytes, uint32_t stages) {
+    SmemLayout l;
+    l.d_stage_bytes = kBlockM * kEpiCols * out_elem_bytes;
+    l.a_stage_bytes = kBlockM * kBlockKBytes;
+    l.b_stage_bytes = b_stage_bytes;
+    l.off_d = 0;
+    l.off_a = 2 * l.d_stage_bytes;
+    l.off_b = l.off_a + stages * l.a_stage_bytes;
+    l.off_bar = l.off_b + stages * l.b_stage_bytes;
+    // full[stages] empty[stages] tmem_full[2] tmem_empty[2] + tmem ptr
+    l.total = l.off_bar + (2 * stages + 4) * 8 + 16;
+    return l;
+}
+
+template <int kCta, typename OutT, bool kBMn>
+__global__ void __launch_bounds__(kNumThreads, 1)
+gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                  const __grid_constant__ CUtensorMap tm_d, const GemmParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
+
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t cta_rank = (kCta == 2) ? ptx::cluster_ctarank() : 0u;
+    const bool is_leader = cta_rank == 0;
+    const uint32_t num_clusters = gridDim.x / kCta;
+    const uint32_t cluster_id = blockIdx.x / kCta;
+    const uint32_t num_tiles = p.num_m_blocks * p.num_n_blocks;
+    const uint32_t stages = p.num_stages;
+
+    const SmemLayout L = make_smem_layout(sizeof(OutT), p.b_stage_bytes, stages);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.off_bar);
+    uint64_t* empty_bar = full_bar + stages;
+    uint64_t* tmem_full_bar = empty_bar + stages;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+    if constexpr (kCta == 2) ptx::cluster_sync();  // peer must be resident before cta_group::2 alloc
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tensormap(&tm_a);
+        ptx::prefetch_tensormap(&tm_b);
+        ptx::prefetch_tensormap(&tm_d);
+    }
+    if (warp == 1 && lane == 0) {
+        for (uint32_t s = 0; s < stages; ++s) {
+            ptx::mbar_init(&full_bar[s], kCta);  // leader expect_tx arrive (+ peer's remote arrive)
+            ptx::mbar_init(&empty_bar[s], 1);    // one tcgen05.commit (multicast to both CTAs)
+        }
+        for (uint32_t s = 0; s < 2; ++s) {
+            ptx::mbar_init(&tmem_full_bar[s], 1);
+            ptx::mbar_init(&tmem_empty_bar[s], kCta * 128);  // every epilogue thread of the pair
+        }
+        ptx::fence_mbar_init();
+    }
+    if (warp == 2) ptx::tmem_alloc<kCta>(tmem_ptr_smem, 512);
+    ptx::tc_fence_before();
+    if constexpr (kCta == 2) ptx::cluster_sync(); else __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    const uint32_t load_n = p.block_n / kCta;  // B rows this CTA loads per stage
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ------------------------------------------------ TMA producer
+            uint32_t stage = 0, phase = 0;
+            for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters) {
+                uint32_t mb, nb;
+                tile_coords(p, t, mb, nb);
+                const int32_t m_idx = static_cast<int32_t>(mb * (kBlockM * kCta) + cta_rank * kBlockM);
+                const int32_t n_idx = static_cast<int32_t>(nb * p.block_n + cta_rank * load_n);
+                for (uint32_t kb = 0; kb < p.k_blocks; ++kb) {
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + L.off_a + stage * L.a_stage_bytes;
+                    uint8_t* sb = smem + L.off_b + stage * L.b_stage_bytes;
+                    const int32_t k_idx = static_cast<int32_t>(kb * 64);
+                    if constexpr (kCta == 2) {
+                        ptx::tma_load_2d_pair(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
+                        if constexpr (kBMn) {
+                            for (uint32_t j = 0; j < load_n / 64; ++j)
+                                ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb + j * 8192, n_idx + j * 64, k_idx);
+                        } else {
+                            ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
+                        }
+                        if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * (L.a_stage_bytes + L.b_stage_bytes));
+                        else ptx::mbar_arrive_remote(&full_bar[stage], 0);
+                    } else {
+                        ptx::tma_load_2d(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
+                        if constexpr (kBMn) {
+                            for (uint32_t j = 0; j < load_n / 64; ++j)
+                                ptx::tma_load_2d(&tm_b, &full_bar[stage], sb + j * 8192, n_idx + j * 64, k_idx);
+                        } else {
+                            ptx::tma_load_2d(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
+                        }
+                        ptx::mbar_arrive_expect_tx(&full_bar[stage], L.a_stage_bytes + L.b_stage_bytes);
+                    }
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0 && is_leader) {
+            // -------------------------------------------------- MMA issuer
+            const uint64_t a_hi = make_smem_desc_hi(1024, kLayoutSw128);
+            // K-major B: 8-row atoms 1024 B apart (SBO).  MN-major B: SBO = 1024 B
+            // between 8-k-row groups, LBO = 8192 B between 64-column groups.
+            const uint64_t b_hi = kBMn ? (make_smem_desc_hi(1024, kLayoutSw128) | (static_cast<uint64_t>(8192 >> 4) << 16))
+                                       : make_smem_desc_hi(1024, kLayoutSw128);
+            const uint32_t a_lo0 = ((smem_base + L.off_a) & 0x3FFFF) >> 4;
+            const uint32_t b_lo0 = ((smem_base + L.off_b) & 0x3FFFF) >> 4;
+            constexpr uint32_t kBStepLo = kBMn ? (16 * 128) >> 4 : 32 >> 4;  // one UMMA_K (16 elements) along K
+            uint32_t stage = 0, phase = 0, iter = 0;
+            for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters, ++iter) {
+                const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
+                ptx::mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t tmem_d = tmem_base + as * p.block_n;
+                for (uint32_t kb = 0; kb < p.k_blocks; ++kb) {
+                    ptx::mbar_wait(&full_bar[stage], phase);
+                    ptx::tc_fence_after();
+                    const uint64_t a_desc = a_hi | (a_lo0 + stage * (L.a_stage_bytes >> 4));
+                    const uint64_t b_desc = b_hi | (b_lo0 + stage * (L.b_stage_bytes >> 4));
+#pragma unroll
+                    for (uint32_t k = 0; k < 4; ++k)
+                        ptx::mma_f16<kCta>(tmem_d, a_desc + k * 2, b_desc + k * kBStepLo, p.idesc, (kb | k) != 0);
+                    ptx::mma_commit<kCta>(&empty_bar[stage]);
+                    if (kb + 1 == p.k_blocks) ptx::mma_commit<kCta>(&tmem_full_bar[as]);
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp >= 4) {
+        // ------------------------------------------------------- epilogue
+        const uint32_t epi_tid = threadIdx.x - 128;          // 0..127 == accumulator row == TMEM lane
+        const uint32_t lane_base = (warp & 3) * 32;          // tcgen05.ld lane window of this warp
+        uint32_t iter = 0, buf = 0;
+        for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters, ++iter) {
+            uint32_t mb, nb;
+            tile_coords(p, t, mb, nb);
+            const uint32_t m0 = mb * (kBlockM * kCta) + cta_rank * kBlockM;
+            const uint32_t n0 = nb * p.block_n;
+            const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
+            // chunks that intersect the matrix (TMA clips a partial last one)
+            const uint32_t n_left = p.n - n0;
+            const uint32_t chunks = min(p.block_n, n_left + kEpiCols - 1) / kEpiCols;
+            ptx::mbar_wait(&tmem_full_bar[as], aphase);
+            ptx::tc_fence_after();
+            const uint32_t taddr = tmem_base + (lane_base << 16) + as * p.block_n;
+            for (uint32_t c = 0; c < chunks; ++c) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32(taddr + c * kEpiCols, v);
+                ptx::tmem_ld_wait();
+                if (c + 1 == chunks) {
+                    // accumulator fully read: hand the TMEM stage back to the issuer
+                    ptx::tc_fence_before();
+                    if constexpr (kCta == 2) ptx::mbar_arrive_remote(&tmem_empty_bar[as], 0);
+                    else ptx::mbar_arrive(&tmem_empty_bar[as]);
+                }
+                // staging buffer `buf` was last read by the store issued two chunks ago
+                if (epi_tid == 0) ptx::tma_store_wait_read<1>();
+                ptx::named_bar_sync(1, 128);
+                const uint32_t sbase = smem_base + L.off_d + buf * L.d_stage_bytes;
+                stage_row<OutT>(sbase, epi_tid, v);
+                ptx::fence_async_smem();
+                ptx::named_bar_sync(1, 128);
+                if (epi_tid == 0) {
+                    if (m0 < p.m)
+                        ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes,
+                                          static_cast<int32_t>(n0 + c * kEpiCols), static_cast<int32_t>(m0));
+                    ptx::tma_store_commit();
+                }
+                buf ^= 1;
+            }
+        }
+        if (epi_tid == 0) ptx::tma_store_wait_all<0>();
+    }
+
+    // ---------------------------------------------------------------- teardown
+    ptx::tc_fence_before();
+    if constexpr (kCta == 2) ptx::cluster_sync(); else __syncthreads();
+    if (warp == 2) ptx::tmem_dealloc<kCta>(tmem_base, 512);
+}
+
+}  // namespace dga

@@ -1,0 +1,184 @@
+// Process-wide plan cache with optional CSV persistence.
+// Role of CatlassTiling::Cache::TilingCache (op_host/op_tiling/cache.cpp:22-101) and CSV::Document
+// (op_tiling/csv.cpp:31-140).  Differences: guarded by a mutex (the reference's singleton is not
+// thread-safe), keyed on (m, n, k, dtype, outDtype, layoutTagB) (the reference keys on (m, n, k) only,
+// "todo: layout tag is key", cache.cpp:47), and the CSV keeps the reference's 11 columns
+// (csv.cpp:23-26) followed by the B200 ones.  First writer wins, like the reference (cache_test.cpp:63-85).
+#include <cstdlib>
+#include <fstream>
+#include <map>
+#include <mutex>
+#include <sstream>
+#include <tuple>
+#include <vector>
+
+#include "tile_selector.h"
+
+namespace dga {
+namespace {
+
+using Key = std::tuple<uint32_t, uint32_t, uint32_t, int32_t, int32_t, int32_t>;
+
+const char* kHeader =
+    "m,n,k,m1,n1,k1,kernelSerial,paddingTagA,paddingTagB,paddingTagC,blockDim,"
+    "ctaGroup,stages,splitkFactor,swizzleOffset,swizzleDirection,dtype,outDtype,layoutTagB";
+constexpr size_t kRefColumns = 11, kAllColumns = 19;
+
+struct Cache {
+    std::mutex mu;
+    std::map<Key, DgaTilingPlan> data;
+    std::string file;  // append target ($CACHE_FILE_PATH), empty = disabled
+    bool env_loaded = false;
+};
+Cache& cache() {
+    static Cache c;
+    return c;
+}
+Key key_of(const DgaTilingPlan& p) { return Key(p.m, p.n, p.k, p.dtype, p.outDtype, p.layoutTagB); }
+
+std::string row_of(const DgaTilingPlan& p) {
+    std::ostringstream os;
+    os << p.m << ',' << p.n << ',' << p.k << ',' << p.m1 << ',' << p.n1 << ',' << p.k1 << ',' << int(p.kernelSerial)
+       << ',' << int(p.paddingTagA) << ',' << int(p.paddingTagB) << ',' << int(p.paddingTagC) << ',' << p.blockDim
+       << ',' << int(p.ctaGroup) << ',' << int(p.stages) << ',' << p.splitkFactor << ',' << int(p.swizzleOffset) << ','
+       << int(p.swizzleDirection) << ',' << int(p.dtype) << ',' << int(p.outDtype) << ',' << int(p.layoutTagB);
+    return os.str();
+}
+
+// Parses one CSV row; accepts the reference's 11-column rows (B200 fields are then re-derived).
+bool parse_row(const std::string& line, DgaTilingPlan& p) {
+    std::vector<long long> v;
+    std::stringstream ss(line);
+    std::string cell;
+    while (std::getline(ss, cell, ',')) {
+        char* end = nullptr;
+        long long x = std::strtoll(cell.c_str(), &end, 10);
+        if (end == cell.c_str()) return false;
+        v.push_back(x);
+    }
+    if (v.size() != kRefColumns && v.size() != kAllColumns) return false;
+    p = DgaTilingPlan{};
+    p.m = uint32_t(v[0]); p.n = uint32_t(v[1]); p.k = uint32_t(v[2]);
+    p.m1 = uint16_t(v[3]); p.n1 = uint16_t(v[4]); p.k1 = uint16_t(v[5]);
+    p.kernelSerial = uint8_t(v[6]);
+    p.paddingTagA = uint8_t(v[7]); p.paddingTagB = uint8_t(v[8]); p.paddingTagC = uint8_t(v[9]);
+    p.blockDim = uint32_t(v[10]);
+    if (v.size() == kAllColumns) {
+        p.ctaGroup = uint8_t(v[11]); p.stages = uint8_t(v[12]); p.splitkFactor = uint16_t(v[13]);
+        p.swizzleOffset = uint8_t(v[14]); p.swizzleDirection = uint8_t(v[15]);
+        p.dtype = uint8_t(v[16]); p.outDtype = uint8_t(v[17]); p.layoutTagB = uint8_t(v[18]);
+    } else {
+        // a reference-format row: Ascend tile sizes are not meaningful here; keep the key, re-select the rest
+        p.dtype = ACL_BF16; p.outDtype = ACL_BF16; p.layoutTagB = 1;
+        DgaTilingPlan q = p;
+        if (select_kernel(q) != ACLNN_SUCCESS) return false;
+        p = q;
+        return true;
+    }
+    p.strideA = p.k;
+    p.strideB = p.layoutTagB ? p.k : p.n;
+    p.strideC = p.n;
+    return finalize_plan(p) == ACLNN_SUCCESS;
+}
+
+int load_csv_locked(Cache& c, const std::string& path) {
+    std::ifstream in(path);
+    if (!in) return ACLNN_ERR_PARAM_INVALID;
+    std::string line;
+    bool first = true;
+    while (std::getline(in, line)) {
+        if (!line.empty() && line.back() == '\r') line.pop_back();
+        if (line.empty()) continue;
+        if (first) {
+            first = false;
+            if (line.rfind("m,n,k", 0) == 0) continue;  // header
+        }
+        DgaTilingPlan p;
+        if (!parse_row(line, p)) {
+            set_error("bad tiling-cache row: " + line);
+            continue;
+        }
+        c.data.emplace(key_of(p), p);  // first writer wins
+    }
+    return ACLNN_SUCCESS;
+}
+
+void ensure_env_loaded(Cache& c) {
+    if (c.env_loaded) return;
+    c.env_loaded = true;
+    const char* path = std::getenv("CACHE_FILE_PATH");  // same variable as the reference (cache.cpp:24)
+    if (path == nullptr || *path == '\0') return;
+    c.file = path;
+    std::ifstream probe(c.file);
+    if (!probe) {
+        std::ofstream out(c.file);
+        if (out) out << kHeader << '\n'; else c.file.clear();
+        return;
+    }
+    probe.close();
+    load_csv_locked(c, c.file);
+}
+
+}  // namespace
+
+int cache_get(DgaTilingPlan& p) {
+    Cache& c = cache();
+    std::lock_guard<std::mutex> g(c.mu);
+    ensure_env_loaded(c);
+    auto it = c.data.find(key_of(p));
+    if (it == c.data.end()) return ACLNN_ERR_PARAM_INVALID;
+    p = it->second;
+    return ACLNN_SUCCESS;
+}
+
+int cache_set(const DgaTilingPlan& p) {
+    Cache& c = cache();
+    std::lock_guard<std::mutex> g(c.mu);
+    ensure_env_loaded(c);
+    if (!c.data.emplace(key_of(p), p).second) return ACLNN_SUCCESS;  // already present: keep the first
+    if (!c.file.empty()) {
+        std::ofstream out(c.file, std::ios::app);
+        if (out) out << row_of(p) << '\n';
+    }
+    return ACLNN_SUCCESS;
+}
+
+void cache_clear() {
+    Cache& c = cache();
+    std::lock_guard<std::mutex> g(c.mu);
+    c.data.clear();
+}
+uint64_t cache_size() {
+    Cache& c = cache();
+    std::lock_guard<std::mutex> g(c.mu);
+    return c.data.size();
+}
+int cache_load_csv(const char* path) {
+    if (path == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    Cache& c = cache();
+    std::lock_guard<std::mutex> g(c.mu);
+    return load_csv_locked(c, path);
+}
+int cache_save_csv(const char* path) {
+    if (path == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    Cache& c = cache();
+    std::lock_guard<std::mutex> g(c.mu);
+    std::ofstream out(path);
+    if (!out) return ACLNN_ERR_PARAM_INVALID;
+    out << kHeader << '\n';
+    for (const auto& kv : c.data) out << row_of(kv.second) << '\n';
+    return ACLNN_SUCCESS;
+}
+
+int select_kernel_with_cache(DgaTilingPlan& p) {
+    DgaTilingPlan hit = p;
+    if (cache_get(hit) == ACLNN_SUCCESS) {
+        p = hit;
+        return ACLNN_SUCCESS;
+    }
+    int rc = select_kernel(p);
+    if (rc == ACLNN_SUCCESS) cache_set(p);
+    return rc;
+}
+
+}  // namespace dga

@@ -1,0 +1,252 @@
+// B200 tile selector.  See tile_selector.h.
+//
+// Decision structure kept from the reference (select_kernel.cpp:333-369):
+//   1. canonicalise degenerate layouts, 2. pick a tile that balances waves over
+//   the cores (BalanceWorkload, utils.cpp:28-40), 3. walk a chain of kernel
+//   variants (Small -> split-K/stream-K -> PaddingCommon -> Common) and take the
+//   first that applies / the cheapest under a cost model.
+// What changed for B200: 148 SMs (74 CTA pairs), tcgen05 tiles of 128*cta x N
+// with N in steps of 16*cta, TMA handles ragged tiles so PADDING_* survives only
+// as "leading dimension not 16-byte aligned -> repack", and the bandwidth
+// polynomial (GetBandwidth, select_kernel.cpp:22-80) becomes a
+// max(tensor, L2 feed, HBM) x wave-quantisation estimate.
+#include "tile_selector.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <iostream>
+
+namespace dga {
+
+PlatformInfo& platform() {
+    static PlatformInfo info;
+    return info;
+}
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) {
+    g_last_error = msg;
+    std::cerr << "[DGA] [ERROR] " << msg << std::endl;
+}
+const char* last_error() { return g_last_error.c_str(); }
+
+uint32_t common_smem_bytes(uint32_t block_n, uint32_t cta_group, uint32_t stages, uint32_t out_bytes,
+                           uint32_t in_bytes) {
+    (void)in_bytes;  // a stage is always one 128-byte swizzle atom along K
+    const uint32_t d_stage = 128 * 32 * out_bytes;
+    const uint32_t a_stage = 128 * 128;
+    const uint32_t b_stage = (block_n / cta_group) * 128;
+    return 2 * d_stage + stages * (a_stage + b_stage) + (2 * stages + 4) * 8 + 16 + 1024;
+}
+
+uint32_t splitk_smem_bytes(uint32_t m_pad, uint32_t stages) {
+    const uint32_t stage = 128 * 128 + m_pad * 128;
+    return stages * stage + (2 * stages + 2) * 8 + 16 + 1024;
+}
+
+namespace {
+
+constexpr double kClockGHz = 1.85;        // tensor peak 2.25 PF = 148 SM x 8192 flop/clk x 1.855 GHz
+constexpr double kL2BytesPerClkSm = 64.0; // sustained L2 -> smem feed per SM
+constexpr double kTileOverheadClk = 1800; // pipeline fill + exposed epilogue per wave
+constexpr double kLaunchUs = 2.0;
+
+struct Cand {
+    uint32_t cta, bn, stages, tiles, grid;
+    double us;
+};
+
+uint32_t max_stages(uint32_t per_stage, uint32_t fixed, uint32_t budget, uint32_t cap) {
+    if (fixed + per_stage > budget) return 0;
+    return std::min<uint32_t>(cap, (budget - fixed) / per_stage);
+}
+
+// Time of the persistent kernel for one (cta_group, block_n).
+Cand eval_common(const DgaTilingPlan& p, uint32_t cta, uint32_t bn) {
+    const PlatformInfo& hw = platform();
+    const uint32_t in_b = elem_bytes(p.dtype), out_b = elem_bytes(p.outDtype);
+    const uint32_t k_elems = 128 / in_b;
+    const uint32_t kb = ceil_div(p.k, k_elems);
+    Cand c{cta, bn, 0, 0, 0, 1e30};
+    const uint32_t fixed = 2 * 128 * 32 * out_b + 1024 + 256;
+    c.stages = max_stages(128 * 128 + (bn / cta) * 128, fixed, hw.smemBytes, 12);
+    if (c.stages < 2) return c;
+    const uint32_t clusters = hw.smCount / cta;
+    c.tiles = ceil_div(p.m, 128 * cta) * ceil_div(p.n, bn);
+    c.grid = std::min(c.tiles, clusters) * cta;
+    const double waves = std::ceil(double(c.tiles) / clusters);
+    // tensor-pipe cycles per 128-byte K block: 4 (fp16) MMAs of 128*cta x bn x 16
+    // (bn/2 clk each, B300_MICROARCH "tcgen05 floor"); an fp8 block holds twice the K in the same 4 MMAs.
+    const double mma_clk = 2.0 * bn;
+    const double feed_clk = (128.0 * 128 + (bn / cta) * 128.0) / kL2BytesPerClkSm;
+    const double tile_clk = kb * std::max(mma_clk, feed_clk) + kTileOverheadClk;
+    const double compute_us = waves * tile_clk / (kClockGHz * 1e3);
+    const double bytes = double(p.m) * p.k * in_b + double(p.n) * p.k * in_b + double(p.m) * p.n * out_b;
+    const double hbm_us = bytes / (hw.hbmGBs * 1e3);
+    c.us = std::max(compute_us, hbm_us) + kLaunchUs;
+    return c;
+}
+
+}  // namespace
+
+static void fill_common(DgaTilingPlan& p, const Cand& c) {
+    const uint32_t in_b = elem_bytes(p.dtype);
+    p.kernelSerial = (c.tiles <= platform().smCount / c.cta) ? DGA_KERNEL_SMALL : DGA_KERNEL_COMMON;
+    p.ctaGroup = static_cast<uint8_t>(c.cta);
+    p.m1 = static_cast<uint16_t>(128 * c.cta);
+    p.n1 = static_cast<uint16_t>(c.bn);
+    p.k1 = static_cast<uint16_t>(128 / in_b);
+    p.stages = static_cast<uint8_t>(c.stages);
+    p.splitkFactor = 1;
+    p.estTimeUs = c.us;
+}
+
+namespace {
+
+// Swap-AB cluster split-K kernel: one CTA owns 128 weight rows x m_pad
+// activations x a K slice; `split` CTAs of a cluster reduce through DSMEM.
+struct SplitCand {
+    uint32_t split, stages, grid;
+    double us;
+};
+
+SplitCand eval_splitk(const DgaTilingPlan& p, uint32_t split) {
+    const PlatformInfo& hw = platform();
+    const uint32_t m_pad = round_up(p.m, 16);
+    const uint32_t kb = ceil_div(p.k, 64);
+    SplitCand c{split, 0, 0, 1e30};
+    if (kb < split) return c;
+    const uint32_t stage = 128 * 128 + m_pad * 128;
+    c.stages = max_stages(stage, 1024 + 256, hw.smemBytes, 12);
+    // the reduce buffer (m_pad x 128 fp32) reuses the ring
+    if (c.stages < 2 || c.stages * stage < m_pad * 512) return c;
+    const uint32_t tiles = ceil_div(p.n, 128);
+    c.grid = tiles * split;
+    // clusters larger than 2 cannot use every SM (GPC granularity)
+    const uint32_t usable = split <= 2 ? hw.smCount : split == 4 ? 132 : 128;
+    const double waves = std::ceil(double(c.grid) / usable);
+    const double kb_per = std::ceil(double(kb) / split);
+    const double cta_bytes = kb_per * stage;
+    const uint32_t active = std::min(c.grid, usable);
+    // each SM streams at most ~1/100 of HBM bandwidth; all active SMs share HBM
+    const double per_sm_gbs = std::min(hw.hbmGBs / active, hw.hbmGBs / 100.0);
+    const double stream_us = waves * cta_bytes / (per_sm_gbs * 1e3);
+    const double mma_us = waves * kb_per * 4 * std::max(m_pad, 32u) / 2.0 / (kClockGHz * 1e3);
+    const double reduce_us = split > 1 ? 1.5 + m_pad * 0.01 * split : 0.5;
+    c.us = std::max(stream_us, mma_us) + reduce_us + kLaunchUs;
+    return c;
+}
+
+bool aligned16(uint64_t elems, uint32_t bytes) { return (elems * bytes) % 16 == 0; }
+
+}  // namespace
+
+int finalize_plan(DgaTilingPlan& p) {
+    const PlatformInfo& hw = platform();
+    const uint32_t in_b = elem_bytes(p.dtype), out_b = elem_bytes(p.outDtype);
+    if (p.kernelSerial == DGA_KERNEL_SPLITK) {
+        const uint32_t m_pad = round_up(p.m, 16);
+        if (m_pad > 256 || p.layoutTagB != 1 || in_b != 2) {
+            set_error("split-K small-M kernel needs m <= 256, 16-bit inputs and a [N,K] weight");
+            return ACLNN_ERR_INNER_TILING_ERROR;
+        }
+        if (p.splitkFactor == 0) p.splitkFactor = 1;
+        if (p.stages == 0) p.stages = static_cast<uint8_t>(max_stages(128 * 128 + m_pad * 128, 1280, hw.smemBytes, 12));
+        p.m1 = static_cast<uint16_t>(m_pad);
+        p.n1 = 128;
+        p.k1 = 64;
+        p.ctaGroup = 1;
+        p.blockDim = ceil_div(p.n, 128) * p.splitkFactor;
+        p.smemBytes = splitk_smem_bytes(m_pad, p.stages);
+        p.workspaceBytes = 0;
+    } else {
+        if (p.ctaGroup != 1 && p.ctaGroup != 2) p.ctaGroup = 2;
+        const uint32_t cta = p.ctaGroup;
+        if (p.n1 == 0 || p.n1 > 256 || p.n1 % (16 * cta) != 0 || (p.layoutTagB == 0 && (p.n1 / cta) % 64 != 0)) {
+            set_error("invalid n1 for the persistent kernel: " + std::to_string(p.n1));
+            return ACLNN_ERR_INNER_TILING_ERROR;
+        }
+        p.m1 = static_cast<uint16_t>(128 * cta);
+        p.k1 = static_cast<uint16_t>(128 / in_b);
+        const uint32_t fixed = 2 * 128 * 32 * out_b + 1024 + 256;
+        const uint32_t cap = max_stages(128 * 128 + (p.n1 / cta) * 128, fixed, hw.smemBytes, 12);
+        if (p.stages == 0 || p.stages > cap) p.stages = static_cast<uint8_t>(cap);
+        if (p.stages < 2) {
+            set_error("tile does not fit shared memory");
+            return ACLNN_ERR_INNER_TILING_ERROR;
+        }
+        const uint32_t tiles = ceil_div(p.m, 128 * cta) * ceil_div(p.n, p.n1);
+        p.blockDim = std::min(tiles, hw.smCount / cta) * cta;
+        p.smemBytes = common_smem_bytes(p.n1, cta, p.stages, out_b, in_b);
+        p.workspaceBytes = 0;
+        if (p.splitkFactor == 0) p.splitkFactor = 1;
+    }
+    if (p.swizzleOffset == 0) p.swizzleOffset = 8;
+    return ACLNN_SUCCESS;
+}
+
+int select_kernel(DgaTilingPlan& p) {
+    if (p.m == 0 || p.n == 0 || p.k == 0) {
+        set_error("empty problem: m, n, k must be positive");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    const uint32_t in_b = elem_bytes(p.dtype), out_b = elem_bytes(p.outDtype);
+    p.layoutTagA = 0;
+    p.layoutTagC = 0;
+    // m == 1 / n == 1 canonicalisation (select_kernel.cpp:340-347): a [K,1] matrix is both row- and
+    // column-major; prefer the K-major reading, which every kernel here supports.
+    if (p.n == 1) p.layoutTagB = 1;
+    p.strideA = p.k;
+    p.strideB = p.layoutTagB ? p.k : p.n;
+    p.strideC = p.n;
+    p.swizzleOffset = 8;
+    p.swizzleDirection = (p.m > p.n) ? 0 : 1;  // tiling_params.h:63-64
+    p.splitkFactor = 1;
+    p.stages = 0;
+    p.paddingTagA = aligned16(p.strideA, in_b) ? 0 : 1;
+    p.paddingTagB = aligned16(p.strideB, in_b) ? 0 : 1;
+    p.paddingTagC = aligned16(p.strideC, out_b) ? 0 : 1;
+
+    // --- persistent kernel candidates (wave balancing over 74 pairs / 148 CTAs)
+    Cand best{0, 0, 0, 0, 0, 1e30};
+    for (uint32_t cta = 2; cta >= 1; --cta) {
+        const uint32_t step = (p.layoutTagB == 0) ? 64 * cta : 16 * cta;
+        for (uint32_t bn = 256; bn >= step && bn >= 32; bn -= step) {
+            if (bn % 32 != 0) continue;  // epilogue works in 32-column chunks
+            Cand c = eval_common(p, cta, bn);
+            // prefer (on ties within 1 %) the pair mode and the larger tile
+            if (c.us < best.us * 0.99) best = c;
+        }
+    }
+    if (best.cta == 0) {
+        set_error("no feasible tile");
+        return ACLNN_ERR_INNER_TILING_ERROR;
+    }
+    // --- small-M swap-AB split-K candidates
+    SplitCand sbest{0, 0, 0, 1e30};
+    if (p.m <= 256 && p.layoutTagB == 1 && in_b == 2) {
+        for (uint32_t s : {1u, 2u, 4u, 8u}) {
+            SplitCand c = eval_splitk(p, s);
+            if (c.us < sbest.us) sbest = c;
+        }
+    }
+    // M <= 64 is HBM-bound by the weight: a 256-row pair tile would waste >= 3/4 of the tensor work and, worse,
+    // most of the SMs' load slots, so the streaming kernel always wins there; above that the estimates decide.
+    if (sbest.split != 0 && (sbest.us < best.us || p.m <= 64)) {
+        p.kernelSerial = DGA_KERNEL_SPLITK;
+        p.splitkFactor = static_cast<uint16_t>(sbest.split);
+        p.stages = static_cast<uint8_t>(sbest.stages);
+        p.estTimeUs = sbest.us;
+    } else {
+        fill_common(p, best);
+    }
+    if (p.paddingTagA || p.paddingTagB || p.paddingTagC) {
+        // PaddingCommon survives only as a leading-dimension repack (padding_common_matmul_kernel.h:64-82)
+        set_error("leading dimension is not 16-byte aligned; stride repack (PADDING_ND) is not built yet");
+        return ACLNN_ERR_INNER_TILING_ERROR;
+    }
+    return finalize_plan(p);
+}
+
+}  // namespace dga

@@ -1,0 +1,56 @@
+// Host tile selector for B200: picks kernel variant, CTA tile, CTA-pair mode,
+// K split, smem ring depth and rasterisation for a runtime (M, N, K).
+// Role of CatlassTiling::SelectKernel + DoTilingLayout* + GetPaddingTag in the
+// reference (op_host/op_tiling/select_kernel.cpp:333-369, do_tiling.cpp:20-204,
+// select_kernel.cpp:82-268).  Pure host C++; no CUDA calls.
+#pragma once
+#include <cstdint>
+#include <string>
+
+#include "../../include/dga_b200.h"
+
+namespace dga {
+
+struct PlatformInfo {
+    uint32_t smCount = 148;
+    uint32_t smemBytes = 232448;  // 227 KB opt-in dynamic shared memory per CTA
+    uint32_t tmemCols = 512;
+    uint64_t l2Bytes = 126ull << 20;
+    double hbmGBs = 6500.0;         // measured copy bandwidth class
+    double denseTflops16 = 1600.0;  // measured cuBLAS burst class
+    double denseTflops8 = 3200.0;
+};
+
+PlatformInfo& platform();
+
+inline uint32_t ceil_div(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
+inline uint32_t round_up(uint32_t a, uint32_t b) { return ceil_div(a, b) * b; }
+inline uint32_t elem_bytes(int32_t dtype) {
+    return dtype == ACL_FLOAT ? 4u : dtype == ACL_FLOAT8_E4M3FN ? 1u : 2u;
+}
+
+// Smem bytes the persistent kernel needs for a (block_n, stages) choice;
+// mirrors make_smem_layout() in gemm_sm100.cuh (+1 KB alignment slack).
+uint32_t common_smem_bytes(uint32_t block_n, uint32_t cta_group, uint32_t stages, uint32_t out_bytes,
+                           uint32_t in_bytes);
+// Smem bytes of the swap-AB split-K kernel (gemm_smallm_sm100.cuh).
+uint32_t splitk_smem_bytes(uint32_t m_pad, uint32_t stages);
+
+// Fills every field of `plan` from (m, n, k, dtype, outDtype, layoutTagB). Returns ACLNN_SUCCESS or an error.
+int select_kernel(DgaTilingPlan& plan);
+// Re-derives grid / smem / workspace for a plan whose tile fields were set by hand (tuning sweeps, CSV rows).
+int finalize_plan(DgaTilingPlan& plan);
+int select_kernel_with_cache(DgaTilingPlan& plan);
+
+// plan_cache.cpp
+int cache_get(DgaTilingPlan& plan);  // keyed by (m, n, k, dtype, outDtype, layoutTagB) already set in `plan`
+int cache_set(const DgaTilingPlan& plan);
+void cache_clear();
+uint64_t cache_size();
+int cache_load_csv(const char* path);
+int cache_save_csv(const char* path);
+
+void set_error(const std::string& msg);
+const char* last_error();
+
+}  // namespace dga

@@ -1,0 +1,144 @@
+"""Torch-facing shim over the C ABI: torch supplies device memory and streams, nothing else.
+
+Mirrors the two call surfaces of the reference:
+  * the aclnn operator CatlassDynamicMatmul(self, mat2) -> out
+    (aclnn_catlass_dynamic_matmul/op_host/catlass_dynamic_matmul.cpp:50-78), two-phase underneath;
+  * the host tiling entry (SelectKernel, op_host/op_tiling/select_kernel.cpp:333-378).
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import lib, check
+
+_DTYPE_TO_ACL = {torch.float32: _lib.ACL_FLOAT, torch.float16: _lib.ACL_FLOAT16, torch.bfloat16: _lib.ACL_BF16}
+if hasattr(torch, "float8_e4m3fn"):
+    _DTYPE_TO_ACL[torch.float8_e4m3fn] = _lib.ACL_FLOAT8_E4M3FN
+
+
+def acl_dtype(dtype):
+    try:
+        return _DTYPE_TO_ACL[dtype]
+    except KeyError:
+        raise TypeError("unsupported dtype %s" % dtype)
+
+
+def acl_tensor(t):
+    """Describe a torch tensor (any strides; nothing is copied, like the reference's IgnoreContiguous inputs)."""
+    d = _lib.AclTensor()
+    d.data = t.data_ptr()
+    d.dtype = acl_dtype(t.dtype)
+    d.ndim = t.dim()
+    for i in range(t.dim()):
+        d.shape[i] = t.shape[i]
+        d.stride[i] = t.stride(i)
+    return d
+
+
+def _stream_ptr(stream=None):
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return ctypes.c_void_p(s.cuda_stream)
+
+
+def _require_cuda(*tensors):
+    for t in tensors:
+        if not t.is_cuda:
+            raise RuntimeError("dga_b200 has no CPU path: tensors must live on a CUDA device")
+
+
+def get_workspace_size(self, mat2, out):
+    """Phase 1: returns (workspace_bytes, executor handle). The handle must go to `execute` or `destroy_executor`."""
+    ws = ctypes.c_uint64(0)
+    ex = ctypes.c_void_p(None)
+    a, b, c = acl_tensor(self), acl_tensor(mat2), acl_tensor(out)
+    check(lib.aclnnCatlassDynamicMatmulGetWorkspaceSize(ctypes.byref(a), ctypes.byref(b), ctypes.byref(c),
+                                                        ctypes.byref(ws), ctypes.byref(ex)),
+          "aclnnCatlassDynamicMatmulGetWorkspaceSize")
+    return ws.value, ex
+
+
+def execute(workspace, workspace_size, executor, stream=None):
+    """Phase 2: asynchronous launch on `stream` (default: torch's current stream)."""
+    ptr = ctypes.c_void_p(workspace.data_ptr()) if workspace is not None else ctypes.c_void_p(None)
+    check(lib.aclnnCatlassDynamicMatmul(ptr, workspace_size, executor, _stream_ptr(stream)),
+          "aclnnCatlassDynamicMatmul")
+
+
+def destroy_executor(executor):
+    lib.dgaDestroyExecutor(executor)
+
+
+def catlass_dynamic_matmul(self, mat2, out=None, stream=None):
+    """out[M,N] = self[M,K] @ mat2[K,N]; fp16/bf16 in, same dtype out, fp32 accumulate.
+
+    mat2 may be the transposed view of a weight stored [N,K] (the reference's layout) or a row-major [K,N].
+    """
+    _require_cuda(self, mat2)
+    if self.dim() != 2 or mat2.dim() != 2:
+        # same rule as InferShape (catlass_dynamic_matmul.cpp:22-26); phase 1 would report it too
+        raise _lib.DgaError(161002, "catlass_dynamic_matmul (inputs must be 2-D)")
+    if out is None:
+        out = torch.empty((self.shape[0], mat2.shape[1]), dtype=self.dtype, device=self.device)
+    ws_bytes, ex = get_workspace_size(self, mat2, out)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=self.device) if ws_bytes else None
+    execute(ws, ws_bytes, ex, stream)
+    return out
+
+
+class Executor:
+    """A repeatable plan: phase 1 once, phase 2 many times (CUDA-graph friendly; role of a cached aclOpExecutor)."""
+
+    def __init__(self, self_t, mat2, out):
+        _require_cuda(self_t, mat2, out)
+        self._keep = (self_t, mat2, out)
+        self.workspace_bytes, self._ex = get_workspace_size(self_t, mat2, out)
+        check(lib.dgaSetExecutorRepeatable(self._ex), "dgaSetExecutorRepeatable")
+        self._ws = torch.empty(self.workspace_bytes, dtype=torch.uint8, device=out.device) \
+            if self.workspace_bytes else None
+
+    def __call__(self, stream=None):
+        execute(self._ws, self.workspace_bytes, self._ex, stream)
+        return self._keep[2]
+
+    def close(self):
+        if self._ex is not None:
+            destroy_executor(self._ex)
+            self._ex = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def select_kernel(m, n, k, dtype=torch.bfloat16, out_dtype=None, layout_b=1, use_cache=False):
+    """Host tiling decision for (m, n, k) as a dict (pure host code, works without a GPU)."""
+    plan = _lib.TilingPlan()
+    fn = lib.dgaSelectKernelWithCache if use_cache else lib.dgaSelectKernel
+    out_dtype = dtype if out_dtype is None else out_dtype
+    check(fn(m, n, k, acl_dtype(dtype), acl_dtype(out_dtype), layout_b, ctypes.byref(plan)), "dgaSelectKernel")
+    return plan.as_dict()
+
+
+def matmul_with_plan(self, mat2, out, stream=None, **fields):
+    """Launch with hand-set plan fields (kernelSerial, ctaGroup, n1, stages, splitkFactor, swizzle*): tuning sweeps."""
+    _require_cuda(self, mat2, out)
+    plan = _lib.TilingPlan()
+    for key, val in fields.items():
+        setattr(plan, key, val)
+    a, b, c = acl_tensor(self), acl_tensor(mat2), acl_tensor(out)
+    check(lib.dgaMatmulWithPlan(ctypes.byref(a), ctypes.byref(b), ctypes.byref(c), ctypes.byref(plan), None, 0,
+                                _stream_ptr(stream)), "dgaMatmulWithPlan")
+    return out
+
+
+def kernel_launch_count():
+    return int(lib.dgaKernelLaunchCount())
+
+
+def nshard_range(n, world_size, rank):
+    b, c = ctypes.c_uint32(0), ctypes.c_uint32(0)
+    check(lib.dgaNShardRange(n, world_size, rank, ctypes.byref(b), ctypes.byref(c)), "dgaNShardRange")
+    return b.value, c.value
