@@ -85,12 +85,7 @@ SIGNATURES = {
 def _load():
     # Rebuild when sources changed (a no-op hash check otherwise). No silent fallback: either the real
     # library loads or the import fails.
-    try:
-        path = _build.build()
-    except Exception:
-        path = _build.LIB_PATH
-        if not os.path.exists(path):
-            raise
+    path = _build.build()
     lib = ctypes.CDLL(path)
     for name, (restype, argtypes) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError here = header/library mismatch

@@ -163,7 +163,7 @@ int finalize_plan(DgaTilingPlan& p) {
     } else {
         if (p.ctaGroup != 1 && p.ctaGroup != 2) p.ctaGroup = 2;
         const uint32_t cta = p.ctaGroup;
-        if (p.n1 == 0 || p.n1 > 256 || p.n1 % (16 * cta) != 0 || (p.layoutTagB == 0 && (p.n1 / cta) % 64 != 0)) {
+        if (p.n1 == 0 || p.n1 > 256 || p.n1 % 32 != 0 || p.n1 % (16 * cta) != 0 || (p.layoutTagB == 0 && (p.n1 / cta) % 64 != 0)) {
             set_error("invalid n1 for the persistent kernel: " + std::to_string(p.n1));
             return ACLNN_ERR_INNER_TILING_ERROR;
         }
