@@ -1,0 +1,201 @@
+"""GPU arm of bench.py (kept separate so that `bench.py --impl reference` never imports torch.cuda or the library)."""
+import json
+import os
+
+import numpy as np
+import torch
+
+import bench as B
+
+
+def _rotation(bytes_per_set):
+    """Enough distinct buffer sets that consecutive steps never find their inputs in the 126 MB L2."""
+    return max(2, int(np.ceil(2.0 * B.L2_BYTES / bytes_per_set)) + 1)
+
+
+def run_ours(args, rank, world):
+    import deepgemm_ascend_b200 as dga   # raises if libdga_b200.so cannot be built/loaded: no fallback
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    shape = B.workload_shape(args.workload, world)
+    m, n, k = shape["m"], shape["n"], shape["k"]
+    if shape["dtype"] == "fp8":
+        from bench_fp8 import run_fp8
+        return run_fp8(args, rank, world, dga, dev, dist)
+    flops, nbytes = B.algorithmic(shape)
+    small_m = m <= 256
+    launches_per_step = 20 if small_m else 1
+    sets = _rotation(nbytes)
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    a_bufs = [torch.randn((m, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
+    w_bufs = [torch.randn((n, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]  # [N,K] slice
+    c_bufs = [torch.empty((m, n), device=dev, dtype=torch.bfloat16) for _ in range(sets)]
+    execs = [dga.Executor(a_bufs[i], w_bufs[i].t(), c_bufs[i]) for i in range(sets)]   # phase 1, once per buffer set
+    plan = dga.select_kernel(m, n, k, use_cache=True)
+
+    stream = torch.cuda.current_stream()
+    graph = None
+    if small_m:
+        # launch latency (~3 us) is a third of the kernel time: replay 20 back-to-back launches as one CUDA graph
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            for i in range(sets):
+                execs[i](side)
+            side.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side):
+                for j in range(launches_per_step):
+                    execs[j % sets](side)
+
+    def step(i):
+        if graph is not None:
+            graph.replay()
+        else:
+            execs[i % sets](stream)
+
+    def fence():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(i)
+    fence()
+    sampler = B.ClockSampler(local)
+    sampler.start()
+    launches0 = dga.kernel_launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    ev[0].record(stream)
+    for i in range(args.steps):
+        step(i)
+        ev[i + 1].record(stream)
+    fence()
+    clocks = sampler.finish()
+    launches = dga.kernel_launch_count() - launches0
+    if graph is not None:
+        launches = args.steps * launches_per_step   # replays do not pass through the host counter
+    total_ms = ev[0].elapsed_time(ev[-1])
+    per_step = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps))
+    t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms_max = float(t.item())
+    n_launch = args.steps * launches_per_step
+    launch_us = total_ms * 1e3 / n_launch
+    value = flops * n_launch * world / (total_ms_max * 1e-3) / 1e12
+
+    # ---- e2e: host buffers in, host buffer out, through the public operator call
+    e2e = e2e_run(dga, dev, m, n, k, steps=max(3, min(args.steps, 10)), flops=flops, world=world, dist=dist)
+
+    # ---- optional: all-gather of C over NVLink (only when the caller needs the full output)
+    gather = None
+    if dist is not None:
+        gather = allgather_run(dist, dev, c_bufs[0], world)
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    peaks = B.measured_peaks()
+    timed_s = total_ms * 1e-3
+    if m <= 128:
+        achieved = nbytes / (launch_us * 1e-6) / 1e9
+        roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "frac": achieved / peaks["hbm_gbs"], "traffic": None,
+                "peak_source": "%s hbm_gbs" % peaks["source"], "frac_of_nominal_8TBs": achieved / B.NOMINAL["hbm_gbs"]}
+    else:
+        which = "bf16_tflops" if timed_s < 1.0 else "bf16_tflops_sustained"
+        achieved = flops / (launch_us * 1e-6) / 1e12
+        roof = {"bound": "tensor", "achieved": achieved, "peak": peaks[which], "unit": "TFLOP/s",
+                "frac": achieved / peaks[which], "traffic": None,
+                "peak_source": "%s %s (timed region %.2f s)" % (peaks["source"], which, timed_s),
+                "frac_of_nominal_2250": achieved / B.NOMINAL["bf16_tflops"]}
+    roof["kernel"] = "gemm_smallm_sm100_kernel" if plan["kernelSerial"] == 3 else "gemm_sm100_kernel"
+    roof["launch_us"] = launch_us
+    roof["algorithmic_bytes"] = nbytes
+    roof["algorithmic_flops"] = flops
+    traffic_path = os.path.join(B.ROOT, "profiles", "traffic_%s.json" % args.workload)
+    if os.path.exists(traffic_path):
+        with open(traffic_path) as f:
+            roof["traffic"] = json.load(f).get("dram_bytes_per_launch")
+    line = {"metric": B.METRIC, "value": value, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms_max / args.steps, "higher_is_better": True,
+            "scaling": shape["scaling"], "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": B.describe(args.workload, shape, world),
+                       "l2_policy": "rotating %d buffer sets (%.0f MB > 2x L2)" % (sets, sets * nbytes / 1e6),
+                       "launches_per_step": launches_per_step,
+                       "plan": {key: plan[key] for key in ("kernelSerial", "ctaGroup", "m1", "n1", "k1", "stages",
+                                                           "splitkFactor", "blockDim")}},
+            "ms_per_step_median": per_step[len(per_step) // 2], "ms_per_step_min": per_step[0],
+            "roofline": roof, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+    if gather is not None:
+        line["allgather"] = gather
+    if not args.no_cpu_baseline:
+        line["cpu_baseline"], _ = B.cpu_golden_run(shape, budget_s=10.0, max_reps=400)
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def e2e_run(dga, dev, m, n, k, steps, flops, world, dist):
+    """Same metric end to end: pinned host A and W -> device, operator call, C -> pinned host, all inside the
+    timed region (CUDA events on the launching stream)."""
+    ha = torch.randn((m, k), dtype=torch.bfloat16).pin_memory()
+    hw = torch.randn((n, k), dtype=torch.bfloat16).pin_memory()
+    hc = torch.empty((m, n), dtype=torch.bfloat16).pin_memory()
+    da, dw = torch.empty_like(ha, device=dev), torch.empty_like(hw, device=dev)
+    dc = torch.empty((m, n), dtype=torch.bfloat16, device=dev)
+    stream = torch.cuda.current_stream()
+
+    def one():
+        da.copy_(ha, non_blocking=True)
+        dw.copy_(hw, non_blocking=True)
+        dga.catlass_dynamic_matmul(da, dw.t(), out=dc)     # two-phase C ABI underneath
+        hc.copy_(dc, non_blocking=True)
+
+    for _ in range(3):
+        one()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(steps):
+        one()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    checksum = float(hc.float().abs().mean())   # the device->host result is really read
+    return {"value": flops * steps * world / (float(ms.item()) * 1e-3) / 1e12, "unit": "TFLOP/s",
+            "h2d_bytes_per_step": int(ha.numel() * 2 + hw.numel() * 2), "d2h_bytes_per_step": int(hc.numel() * 2),
+            "steps": steps, "result_abs_mean": checksum}
+
+
+def allgather_run(dist, dev, c_local, world):
+    """NCCL all-gather of the rank's C slice into a [g, M, N/g] staging buffer (contiguous messages)."""
+    full = torch.empty((world,) + tuple(c_local.shape), dtype=c_local.dtype, device=dev)
+    for _ in range(3):
+        dist.all_gather_into_tensor(full, c_local)
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 10
+    e0.record()
+    for _ in range(reps):
+        dist.all_gather_into_tensor(full, c_local)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / reps], device=dev, dtype=torch.float64)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    recv = c_local.numel() * c_local.element_size() * (world - 1)
+    return {"ms": float(ms.item()), "recv_bytes_per_rank": int(recv),
+            "recv_GBs_per_rank": recv / (float(ms.item()) * 1e-3) / 1e9}

@@ -11,6 +11,7 @@
 #include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 
@@ -91,9 +92,16 @@ struct DenseLaunch {
     bool encoded = false;
 };
 
+// cudaFuncSetAttribute costs microseconds of host time; remember the largest opt-in per kernel instance.
 template <typename K>
 static int set_smem_attr(K kernel, uint32_t bytes) {
+    static std::mutex mu;
+    static std::map<const void*, uint32_t> granted;
+    std::lock_guard<std::mutex> lock(mu);
+    uint32_t& have = granted[reinterpret_cast<const void*>(kernel)];
+    if (bytes <= have) return ACLNN_SUCCESS;
     DGA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
+    have = bytes;
     return ACLNN_SUCCESS;
 }
 
