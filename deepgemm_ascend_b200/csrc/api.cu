@@ -10,6 +10,7 @@
 
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -172,6 +173,8 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream) {
     gp.raster_along_m = p.swizzleDirection;
     gp.idesc = make_idesc(128 * cta, p.n1, p.dtype == ACL_BF16 ? 1u : 0u, 0, p.layoutTagB == 1 ? 0u : 1u);
     gp.b_stage_bytes = (p.n1 / cta) * 128;
+    static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
+    gp.debug = dbg;
     if (cta == 2)
         return p.layoutTagB == 1 ? launch_common_out<2, false>(L, gp, stream) : launch_common_out<2, true>(L, gp, stream);
     return p.layoutTagB == 1 ? launch_common_out<1, false>(L, gp, stream) : launch_common_out<1, true>(L, gp, stream);

@@ -44,6 +44,7 @@ struct GemmParams {
     uint32_t raster_along_m; // 1: consecutive tiles walk M inside a group of N blocks (role of swizzleDirection)
     uint32_t idesc;          // tcgen05 instruction descriptor
     uint32_t b_stage_bytes;  // bytes of B per CTA per stage
+    uint32_t debug;          // bottleneck isolation (DGA_DEBUG_FLAGS): 1 no TMA loads, 2 no MMAs, 4 no stores
 };
 
 // --- descriptors -----------------------------------------------------------
@@ -198,16 +199,23 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     const uint32_t load_n = p.block_n / kCta;  // B rows this CTA loads per stage
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ------------------------------------------------ TMA producer
-            uint32_t stage = 0, phase = 0;
-            for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters) {
-                uint32_t mb, nb;
-                tile_coords(p, t, mb, nb);
-                const int32_t m_idx = static_cast<int32_t>(mb * (kBlockM * kCta) + cta_rank * kBlockM);
-                const int32_t n_idx = static_cast<int32_t>(nb * p.block_n + cta_rank * load_n);
-                for (uint32_t kb = 0; kb < p.k_blocks; ++kb) {
-                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+        // ------------------------------------------------ TMA producer
+        // The whole warp walks the loop converged (uniform registers hold the addresses); one elected
+        // lane issues.  A divergent `lane == 0` loop costs an ELECT/R2UR shuffle per operand.
+        uint32_t stage = 0, phase = 0;
+        for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters) {
+            uint32_t mb, nb;
+            tile_coords(p, t, mb, nb);
+            const int32_t m_idx = static_cast<int32_t>(mb * (kBlockM * kCta) + cta_rank * kBlockM);
+            const int32_t n_idx = static_cast<int32_t>(nb * p.block_n + cta_rank * load_n);
+            for (uint32_t kb = 0; kb < p.k_blocks; ++kb) {
+                ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                if (p.debug & 1) {
+                    if (ptx::elect_one()) {
+                        if (is_leader) ptx::mbar_arrive(&full_bar[stage]);
+                        else ptx::mbar_arrive_remote(&full_bar[stage], 0);
+                    }
+                } else if (ptx::elect_one()) {
                     uint8_t* sa = smem + L.off_a + stage * L.a_stage_bytes;
                     uint8_t* sb = smem + L.off_b + stage * L.b_stage_bytes;
                     const int32_t k_idx = static_cast<int32_t>(kb * 64);
@@ -231,43 +239,53 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                         }
                         ptx::mbar_arrive_expect_tx(&full_bar[stage], L.a_stage_bytes + L.b_stage_bytes);
                     }
-                    if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
+                __syncwarp();
+                if (++stage == stages) { stage = 0; phase ^= 1; }
             }
         }
-        __syncwarp();
     } else if (warp == 1) {
-        if (lane == 0 && is_leader) {
-            // -------------------------------------------------- MMA issuer
-            const uint64_t a_hi = make_smem_desc_hi(1024, kLayoutSw128);
+        if (is_leader) {
+            // -------------------------------------------------- MMA issuer (warp-converged, one lane issues)
+            // Only the low 32 bits of a descriptor change (14-bit start address field): keep the high
+            // halves constant and do 32-bit arithmetic.
+            const uint32_t a_hi = static_cast<uint32_t>(make_smem_desc_hi(1024, kLayoutSw128) >> 32);
+            const uint32_t b_hi = a_hi;
             // K-major B: 8-row atoms 1024 B apart (SBO).  MN-major B: SBO = 1024 B
             // between 8-k-row groups, LBO = 8192 B between 64-column groups.
-            const uint64_t b_hi = kBMn ? (make_smem_desc_hi(1024, kLayoutSw128) | (static_cast<uint64_t>(8192 >> 4) << 16))
-                                       : make_smem_desc_hi(1024, kLayoutSw128);
+            const uint32_t b_lbo = kBMn ? ((8192u >> 4) << 16) : 0u;
             const uint32_t a_lo0 = ((smem_base + L.off_a) & 0x3FFFF) >> 4;
-            const uint32_t b_lo0 = ((smem_base + L.off_b) & 0x3FFFF) >> 4;
+            const uint32_t b_lo0 = (((smem_base + L.off_b) & 0x3FFFF) >> 4) | b_lbo;
+            const uint32_t a_step = L.a_stage_bytes >> 4, b_step = L.b_stage_bytes >> 4;
             constexpr uint32_t kBStepLo = kBMn ? (16 * 128) >> 4 : 32 >> 4;  // one UMMA_K (16 elements) along K
+            const uint32_t idesc = p.idesc;
+            const uint32_t k_blocks = p.k_blocks;
             uint32_t stage = 0, phase = 0, iter = 0;
             for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters, ++iter) {
                 const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
                 ptx::mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
                 ptx::tc_fence_after();
                 const uint32_t tmem_d = tmem_base + as * p.block_n;
-                for (uint32_t kb = 0; kb < p.k_blocks; ++kb) {
+                for (uint32_t kb = 0; kb < k_blocks; ++kb) {
                     ptx::mbar_wait(&full_bar[stage], phase);
                     ptx::tc_fence_after();
-                    const uint64_t a_desc = a_hi | (a_lo0 + stage * (L.a_stage_bytes >> 4));
-                    const uint64_t b_desc = b_hi | (b_lo0 + stage * (L.b_stage_bytes >> 4));
+                    if (ptx::elect_one()) {
+                        const uint32_t a_lo = a_lo0 + stage * a_step;
+                        const uint32_t b_lo = b_lo0 + stage * b_step;
 #pragma unroll
-                    for (uint32_t k = 0; k < 4; ++k)
-                        ptx::mma_f16<kCta>(tmem_d, a_desc + k * 2, b_desc + k * kBStepLo, p.idesc, (kb | k) != 0);
-                    ptx::mma_commit<kCta>(&empty_bar[stage]);
-                    if (kb + 1 == p.k_blocks) ptx::mma_commit<kCta>(&tmem_full_bar[as]);
+                        for (uint32_t k = 0; k < 4; ++k) {
+                            const uint64_t a_desc = (static_cast<uint64_t>(a_hi) << 32) | (a_lo + k * 2);
+                            const uint64_t b_desc = (static_cast<uint64_t>(b_hi) << 32) | (b_lo + k * kBStepLo);
+                            if (!(p.debug & 2)) ptx::mma_f16<kCta>(tmem_d, a_desc, b_desc, idesc, (kb | k) != 0);
+                        }
+                        ptx::mma_commit<kCta>(&empty_bar[stage]);
+                        if (kb + 1 == k_blocks) ptx::mma_commit<kCta>(&tmem_full_bar[as]);
+                    }
+                    __syncwarp();
                     if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
             }
         }
-        __syncwarp();
     } else if (warp >= 4) {
         // ------------------------------------------------------- epilogue
         const uint32_t epi_tid = threadIdx.x - 128;          // 0..127 == accumulator row == TMEM lane
@@ -303,7 +321,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                 ptx::fence_async_smem();
                 ptx::named_bar_sync(1, 128);
                 if (epi_tid == 0) {
-                    if (m0 < p.m)
+                    if (m0 < p.m && !(p.debug & 4))
                         ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes,
                                           static_cast<int32_t>(n0 + c * kEpiCols), static_cast<int32_t>(m0));
                     ptx::tma_store_commit();
