@@ -25,19 +25,28 @@ def run_ours(args, rank, world):
 
     shape = B.workload_shape(args.workload, world)
     m, n, k = shape["m"], shape["n"], shape["k"]
-    if shape["dtype"] == "fp8":
-        from bench_fp8 import run_fp8
-        return run_fp8(args, rank, world, dga, dev, dist)
+    fp8 = shape["dtype"] == "fp8"
     flops, nbytes = B.algorithmic(shape)
-    small_m = m <= 256
+    small_m = m <= 256 and not fp8
     launches_per_step = 20 if small_m else 1
     sets = _rotation(nbytes)
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
-    a_bufs = [torch.randn((m, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
-    w_bufs = [torch.randn((n, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]  # [N,K] slice
-    c_bufs = [torch.empty((m, n), device=dev, dtype=torch.bfloat16) for _ in range(sets)]
-    execs = [dga.Executor(a_bufs[i], w_bufs[i].t(), c_bufs[i]) for i in range(sets)]   # phase 1, once per buffer set
-    plan = dga.select_kernel(m, n, k, use_cache=True)
+    if fp8:
+        def quant(rows):
+            x = torch.randn((rows, k), device=dev, generator=gen)
+            return x.to(torch.float8_e4m3fn)
+        a_bufs = [quant(m) for _ in range(sets)]
+        w_bufs = [quant(n) for _ in range(sets)]
+        sa = [torch.rand((m, -(-k // 128)), device=dev, generator=gen) + 0.5 for _ in range(sets)]
+        sw = [torch.rand((-(-n // 128), -(-k // 128)), device=dev, generator=gen) + 0.5 for _ in range(sets)]
+        c_bufs = [torch.empty((m, n), device=dev, dtype=torch.bfloat16) for _ in range(sets)]
+        execs = [dga.Fp8Executor(a_bufs[i], sa[i], w_bufs[i], sw[i], c_bufs[i]) for i in range(sets)]
+    else:
+        a_bufs = [torch.randn((m, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
+        w_bufs = [torch.randn((n, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]  # [N,K]
+        c_bufs = [torch.empty((m, n), device=dev, dtype=torch.bfloat16) for _ in range(sets)]
+        execs = [dga.Executor(a_bufs[i], w_bufs[i].t(), c_bufs[i]) for i in range(sets)]   # phase 1, once per set
+    plan = dga.select_kernel(m, n, k, use_cache=True) if not fp8 else {"kernelSerial": 0}
 
     stream = torch.cuda.current_stream()
     graph = None
@@ -92,7 +101,7 @@ def run_ours(args, rank, world):
     value = flops * n_launch * world / (total_ms_max * 1e-3) / 1e12
 
     # ---- e2e: host buffers in, host buffer out, through the public operator call
-    e2e = e2e_run(dga, dev, m, n, k, steps=max(3, min(args.steps, 10)), flops=flops, world=world, dist=dist)
+    e2e = e2e_run(dga, dev, m, n, k, steps=max(3, min(args.steps, 10)), flops=flops, world=world, dist=dist, fp8=fp8)
 
     # ---- optional: all-gather of C over NVLink (only when the caller needs the full output)
     gather = None
@@ -105,7 +114,7 @@ def run_ours(args, rank, world):
         return
     peaks = B.measured_peaks()
     timed_s = total_ms * 1e-3
-    if m <= 128:
+    if m <= 128 and not fp8:
         achieved = nbytes / (launch_us * 1e-6) / 1e9
         roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": achieved / peaks["hbm_gbs"], "traffic": None,
@@ -113,11 +122,15 @@ def run_ours(args, rank, world):
     else:
         which = "bf16_tflops" if timed_s < 1.0 else "bf16_tflops_sustained"
         achieved = flops / (launch_us * 1e-6) / 1e12
-        roof = {"bound": "tensor", "achieved": achieved, "peak": peaks[which], "unit": "TFLOP/s",
-                "frac": achieved / peaks[which], "traffic": None,
-                "peak_source": "%s %s (timed region %.2f s)" % (peaks["source"], which, timed_s),
-                "frac_of_nominal_2250": achieved / B.NOMINAL["bf16_tflops"]}
-    roof["kernel"] = "gemm_smallm_sm100_kernel" if plan["kernelSerial"] == 3 else "gemm_sm100_kernel"
+        # no fp8 figure is measured by the driver: the fp8 tensor rate is exactly 2x the bf16 one on this part
+        peak = peaks[which] * (2.0 if fp8 else 1.0)
+        roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                "frac": achieved / peak, "traffic": None,
+                "peak_source": "%s %s%s (timed region %.2f s)" % (peaks["source"], which, " x2 for fp8" if fp8 else "",
+                                                                  timed_s),
+                "frac_of_nominal": achieved / (B.NOMINAL["fp8_tflops"] if fp8 else B.NOMINAL["bf16_tflops"])}
+    roof["kernel"] = "gemm_fp8_sm100_kernel" if fp8 else \
+        "gemm_smallm_sm100_kernel" if plan["kernelSerial"] == 3 else "gemm_sm100_kernel"
     roof["launch_us"] = launch_us
     roof["algorithmic_bytes"] = nbytes
     roof["algorithmic_flops"] = flops
@@ -127,12 +140,13 @@ def run_ours(args, rank, world):
             roof["traffic"] = json.load(f).get("dram_bytes_per_launch")
     line = {"metric": B.METRIC, "value": value, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms_max / args.steps, "higher_is_better": True,
-            "scaling": shape["scaling"], "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "scaling": shape["scaling"], "vs_baseline": None, "dtype": "fp8_e4m3" if fp8 else "bf16",
+            "data": "synthetic",
             "config": {"workload": B.describe(args.workload, shape, world),
                        "l2_policy": "rotating %d buffer sets (%.0f MB > 2x L2)" % (sets, sets * nbytes / 1e6),
                        "launches_per_step": launches_per_step,
-                       "plan": {key: plan[key] for key in ("kernelSerial", "ctaGroup", "m1", "n1", "k1", "stages",
-                                                           "splitkFactor", "blockDim")}},
+                       "plan": {key: plan.get(key) for key in ("kernelSerial", "ctaGroup", "m1", "n1", "k1", "stages",
+                                                               "splitkFactor", "blockDim")}},
             "ms_per_step_median": per_step[len(per_step) // 2], "ms_per_step_min": per_step[0],
             "roofline": roof, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
     if gather is not None:
@@ -144,20 +158,32 @@ def run_ours(args, rank, world):
         dist.destroy_process_group()
 
 
-def e2e_run(dga, dev, m, n, k, steps, flops, world, dist):
+def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False):
     """Same metric end to end: pinned host A and W -> device, operator call, C -> pinned host, all inside the
     timed region (CUDA events on the launching stream)."""
-    ha = torch.randn((m, k), dtype=torch.bfloat16).pin_memory()
-    hw = torch.randn((n, k), dtype=torch.bfloat16).pin_memory()
+    in_dtype = torch.float8_e4m3fn if fp8 else torch.bfloat16
+    ha = torch.randn((m, k)).to(in_dtype).pin_memory()
+    hw = torch.randn((n, k)).to(in_dtype).pin_memory()
     hc = torch.empty((m, n), dtype=torch.bfloat16).pin_memory()
     da, dw = torch.empty_like(ha, device=dev), torch.empty_like(hw, device=dev)
     dc = torch.empty((m, n), dtype=torch.bfloat16, device=dev)
+    extra = 0
+    if fp8:
+        hsa = (torch.rand((m, -(-k // 128))) + 0.5).pin_memory()
+        hsw = (torch.rand((-(-n // 128), -(-k // 128))) + 0.5).pin_memory()
+        dsa, dsw = torch.empty_like(hsa, device=dev), torch.empty_like(hsw, device=dev)
+        extra = hsa.numel() * 4 + hsw.numel() * 4
     stream = torch.cuda.current_stream()
 
     def one():
         da.copy_(ha, non_blocking=True)
         dw.copy_(hw, non_blocking=True)
-        dga.catlass_dynamic_matmul(da, dw.t(), out=dc)     # two-phase C ABI underneath
+        if fp8:
+            dsa.copy_(hsa, non_blocking=True)
+            dsw.copy_(hsw, non_blocking=True)
+            dga.fp8_block_scaled_matmul(da, dsa, dw, dsw, out=dc)
+        else:
+            dga.catlass_dynamic_matmul(da, dw.t(), out=dc)     # two-phase C ABI underneath
         hc.copy_(dc, non_blocking=True)
 
     for _ in range(3):
@@ -176,7 +202,7 @@ def e2e_run(dga, dev, m, n, k, steps, flops, world, dist):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     checksum = float(hc.float().abs().mean())   # the device->host result is really read
     return {"value": flops * steps * world / (float(ms.item()) * 1e-3) / 1e12, "unit": "TFLOP/s",
-            "h2d_bytes_per_step": int(ha.numel() * 2 + hw.numel() * 2), "d2h_bytes_per_step": int(hc.numel() * 2),
+            "h2d_bytes_per_step": int((ha.numel() + hw.numel()) * ha.element_size() + extra), "d2h_bytes_per_step": int(hc.numel() * 2),
             "steps": steps, "result_abs_mean": checksum}
 
 

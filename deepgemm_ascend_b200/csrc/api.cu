@@ -17,6 +17,7 @@
 #include <string>
 
 #include "gemm_smallm_sm100.cuh"
+#include "gemm_fp8_sm100.cuh"
 #include "tile_selector.h"
 
 namespace dga {
@@ -250,6 +251,97 @@ static int launch_dense(DenseLaunch& L, cudaStream_t stream) {
     return ACLNN_ERR_INNER_TILING_ERROR;
 }
 
+// ---- fp8 e4m3 block-scaled -------------------------------------------------------------------------------
+struct Fp8Launch {
+    uint32_t m = 0, n = 0, k = 0, cta = 2, bn = 256, stages = 0, grid = 0, smem = 0;
+    const void* a = nullptr; const void* b = nullptr; void* d = nullptr;
+    const float* sfa = nullptr; const float* sfb = nullptr;
+    uint64_t lda = 0, ldb = 0, ldd = 0, sfa_ld = 0, sfb_ld = 0;
+    CUtensorMap tm_a, tm_b, tm_d;
+    bool encoded = false;
+};
+
+static const uint32_t kFp8TilesPair[] = {256, 224, 192, 128};
+
+// Wave-balanced tile for the fp8 kernel: fewest (waves x block_n) column-units, ties to the wider tile.
+static void plan_fp8(Fp8Launch& L) {
+    const PlatformInfo& hw = platform();
+    if (L.m <= 128) {
+        L.cta = 1; L.bn = 128;
+    } else {
+        L.cta = 2;
+        uint64_t best = ~0ull;
+        for (uint32_t bn : kFp8TilesPair) {
+            const uint64_t tiles = uint64_t(ceil_div(L.m, 256)) * ceil_div(L.n, bn);
+            const uint64_t waves = (tiles + hw.smCount / 2 - 1) / (hw.smCount / 2);
+            const uint64_t cost = waves * bn;
+            if (cost < best) { best = cost; L.bn = bn; }
+        }
+    }
+    const uint32_t per_stage = 128 * 128 + (L.bn / L.cta) * 128;
+    const uint32_t fixed = 4 * 128 * 32 * 2 + 1024 + 256;
+    L.stages = std::min<uint32_t>(10, (hw.smemBytes - fixed) / per_stage);
+    const uint32_t tiles = ceil_div(L.m, 128 * L.cta) * ceil_div(L.n, L.bn);
+    L.grid = std::min(tiles, hw.smCount / L.cta) * L.cta;
+    L.smem = make_fp8_smem(L.bn, L.cta, L.stages).total + 1024;
+}
+
+template <int kCta, uint32_t kBN>
+static int launch_fp8_inst(const Fp8Launch& L, const Fp8Params& fp, cudaStream_t stream) {
+    auto kernel = gemm_fp8_sm100_kernel<kCta, kBN>;
+    int rc = set_smem_attr(kernel, L.smem);
+    if (rc != ACLNN_SUCCESS) return rc;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(L.grid);
+    cfg.blockDim = dim3(kFp8Threads);
+    cfg.dynamicSmemBytes = L.smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kCta;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, fp));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return ACLNN_SUCCESS;
+}
+
+static int launch_fp8(Fp8Launch& L, cudaStream_t stream) {
+    if (!L.encoded) {
+        int rc = make_tmap_2d(&L.tm_a, L.a, ACL_FLOAT8_E4M3FN, L.k, L.m, L.lda, 128, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc != ACLNN_SUCCESS) return rc;
+        rc = make_tmap_2d(&L.tm_b, L.b, ACL_FLOAT8_E4M3FN, L.k, L.n, L.ldb, 128, L.bn / L.cta, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc != ACLNN_SUCCESS) return rc;
+        rc = make_tmap_2d(&L.tm_d, L.d, ACL_BF16, L.n, L.m, L.ldd, 32, 128, CU_TENSOR_MAP_SWIZZLE_64B);
+        if (rc != ACLNN_SUCCESS) return rc;
+        L.encoded = true;
+    }
+    Fp8Params fp{};
+    fp.m = L.m; fp.n = L.n; fp.k = L.k;
+    fp.block_n = L.bn;
+    fp.num_stages = L.stages;
+    fp.k_blocks = ceil_div(L.k, 128);
+    fp.num_m_blocks = ceil_div(L.m, 128 * L.cta);
+    fp.num_n_blocks = ceil_div(L.n, L.bn);
+    fp.raster_group = 8;
+    fp.raster_along_m = L.m > L.n ? 0 : 1;
+    fp.idesc = make_idesc(128 * L.cta, L.bn, 0u, 0, 0);
+    fp.sfa_ld = uint32_t(L.sfa_ld); fp.sfb_ld = uint32_t(L.sfb_ld);
+    fp.sfb_rows = ceil_div(L.n, 128);
+    fp.sfa = L.sfa; fp.sfb = L.sfb;
+    if (L.cta == 1) return launch_fp8_inst<1, 128>(L, fp, stream);
+    switch (L.bn) {
+        case 256: return launch_fp8_inst<2, 256>(L, fp, stream);
+        case 224: return launch_fp8_inst<2, 224>(L, fp, stream);
+        case 192: return launch_fp8_inst<2, 192>(L, fp, stream);
+        case 128: return launch_fp8_inst<2, 128>(L, fp, stream);
+    }
+    set_error("fp8 tile not instantiated");
+    return ACLNN_ERR_INNER_TILING_ERROR;
+}
+
 __global__ void mmad_custom_stub(const void*, const void*, void*) {}
 
 }  // namespace dga
@@ -259,6 +351,8 @@ using namespace dga;
 
 struct aclOpExecutor {
     DenseLaunch dense;
+    Fp8Launch fp8;
+    bool is_fp8 = false;
     bool repeatable = false;
 };
 
@@ -383,8 +477,8 @@ aclnnStatus aclnnCatlassDynamicMatmulGetWorkspaceSize(const aclTensor* self, con
 
 aclnnStatus aclnnCatlassDynamicMatmul(void* workspace, uint64_t workspaceSize, aclOpExecutor* executor,
                                       aclrtStream stream) {
-    if (executor == nullptr) {
-        set_error("null executor");
+    if (executor == nullptr || executor->is_fp8) {
+        set_error("null or mismatched executor");
         return ACLNN_ERR_PARAM_NULLPTR;
     }
     aclnnStatus rc = ACLNN_SUCCESS;
@@ -427,15 +521,74 @@ aclnnStatus dgaMatmulWithPlan(const aclTensor* self, const aclTensor* mat2, cons
     return launch_dense(L, static_cast<cudaStream_t>(stream));
 }
 
-// ---- fp8 block-scaled (filled in by gemm_fp8_sm100.cuh) ------------------------------------------------
-aclnnStatus dgaFp8BlockScaledMatmulGetWorkspaceSize(const aclTensor*, const aclTensor*, const aclTensor*,
-                                                    const aclTensor*, const aclTensor*, uint64_t*, aclOpExecutor**) {
-    set_error("fp8 block-scaled kernel is not built yet");
-    return ACLNN_ERR_INNER_TILING_ERROR;
+// ---- fp8 block-scaled ------------------------------------------------------------------------------------
+aclnnStatus dgaFp8BlockScaledMatmulGetWorkspaceSize(const aclTensor* self, const aclTensor* selfScale,
+                                                    const aclTensor* mat2, const aclTensor* mat2Scale,
+                                                    const aclTensor* out, uint64_t* workspaceSize,
+                                                    aclOpExecutor** executor) {
+    if (!self || !selfScale || !mat2 || !mat2Scale || !out || !workspaceSize || !executor) {
+        set_error("null argument");
+        return ACLNN_ERR_PARAM_NULLPTR;
+    }
+    if (self->ndim != 2 || mat2->ndim != 2 || out->ndim != 2 || selfScale->ndim != 2 || mat2Scale->ndim != 2) {
+        set_error("Invalid input dimensions. all tensors must be 2-D");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (self->dtype != ACL_FLOAT8_E4M3FN || mat2->dtype != ACL_FLOAT8_E4M3FN || selfScale->dtype != ACL_FLOAT ||
+        mat2Scale->dtype != ACL_FLOAT || out->dtype != ACL_BF16) {
+        set_error("fp8 matmul wants e4m3 operands, float32 scales and a bfloat16 output");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    const int64_t m = self->shape[0], k = self->shape[1], n = mat2->shape[1];
+    if (mat2->shape[0] != k) {
+        set_error("K dimension mismatch: self[1]=" + std::to_string(k) + " mat2[0]=" + std::to_string(mat2->shape[0]));
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (m <= 0 || n <= 0 || k <= 0 || m > UINT32_MAX || n > UINT32_MAX || k > UINT32_MAX || out->shape[0] != m ||
+        out->shape[1] != n) {
+        set_error("bad extents");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    const int64_t kb = (k + 127) / 128, nb = (n + 127) / 128;
+    if (selfScale->shape[0] != m || selfScale->shape[1] != kb || mat2Scale->shape[0] != nb || mat2Scale->shape[1] != kb) {
+        set_error("scale shapes must be [M, ceil(K/128)] and [ceil(N/128), ceil(K/128)]");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if ((self->stride[1] != 1 && k != 1) || mat2->stride[0] != 1 || (out->stride[1] != 1 && n != 1) ||
+        (selfScale->stride[1] != 1 && kb != 1) || (mat2Scale->stride[1] != 1 && kb != 1)) {
+        set_error("fp8 matmul layout: self row-major, mat2 column-major (weight stored [N,K]), scales and out row-major");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    aclOpExecutor* ex = new aclOpExecutor{};
+    ex->is_fp8 = true;
+    Fp8Launch& L = ex->fp8;
+    L.m = uint32_t(m); L.n = uint32_t(n); L.k = uint32_t(k);
+    L.a = self->data; L.b = mat2->data; L.d = out->data;
+    L.sfa = static_cast<const float*>(selfScale->data);
+    L.sfb = static_cast<const float*>(mat2Scale->data);
+    L.lda = m == 1 ? uint64_t(k) : uint64_t(self->stride[0]);
+    L.ldb = n == 1 ? uint64_t(k) : uint64_t(mat2->stride[1]);
+    L.ldd = m == 1 ? uint64_t(n) : uint64_t(out->stride[0]);
+    L.sfa_ld = m == 1 ? uint64_t(kb) : uint64_t(selfScale->stride[0]);
+    L.sfb_ld = nb == 1 ? uint64_t(kb) : uint64_t(mat2Scale->stride[0]);
+    if (L.lda % 16 || L.ldb % 16 || (L.ldd * 2) % 16) {
+        set_error("leading dimensions must be 16-byte aligned");
+        delete ex;
+        return ACLNN_ERR_INNER_TILING_ERROR;
+    }
+    plan_fp8(L);
+    *workspaceSize = 0;
+    *executor = ex;
+    return ACLNN_SUCCESS;
 }
-aclnnStatus dgaFp8BlockScaledMatmul(void*, uint64_t, aclOpExecutor*, aclrtStream) {
-    set_error("fp8 block-scaled kernel is not built yet");
-    return ACLNN_ERR_INNER_TILING_ERROR;
+aclnnStatus dgaFp8BlockScaledMatmul(void*, uint64_t, aclOpExecutor* executor, aclrtStream stream) {
+    if (executor == nullptr || !executor->is_fp8) {
+        set_error("not an fp8 executor");
+        return ACLNN_ERR_PARAM_NULLPTR;
+    }
+    aclnnStatus rc = launch_fp8(executor->fp8, static_cast<cudaStream_t>(stream));
+    if (!executor->repeatable) delete executor;
+    return rc;
 }
 
 // ---- host tiling -------------------------------------------------------------------------------------

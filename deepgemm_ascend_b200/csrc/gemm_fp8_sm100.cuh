@@ -1,0 +1,293 @@
+// fp8 e4m3 block-scaled GEMM for sm_100a, DeepGEMM semantics:
+//   D[m,n] (bf16) = sum_kb  sfa[m,kb] * sfb[n/128,kb] * ( sum_{k in block kb} A[m,k] * B[n,k] )
+// A [M,K] e4m3 with one fp32 scale per 1x128 strip, B [N,K] e4m3 with one fp32 scale per 128x128 block.
+// Not in the reference (BASELINE.json north_star item 1).  The scales are arbitrary fp32 values, so they
+// cannot ride in the instruction (kind::mxf8f6f4 block scaling wants UE8M0): every 128-wide K block is a
+// separate tcgen05 accumulation (kind::f8f6f4, fp32) into one of two TMEM buffers, and the promotion warps
+// pull it out (tcgen05.ld), multiply by sfa*sfb and add it to fp32 accumulators held in REGISTERS.
+//
+//   warp 0        : TMA producer          (A/B tiles -> smem ring, SWIZZLE_128B, 128 fp8 = 128 B per row)
+//   warp 1        : MMA issuer            (4 x K=32 MMAs per K block; commit -> ring slot + partial buffer)
+//   warp 2        : TMEM alloc / dealloc
+//   warps 4..11   : promotion + epilogue  (2 warp groups; group g owns the 32-column chunks c = g, g+2, ...)
+// While the promotion of block kb runs from buffer kb&1, the tensor core fills the other buffer with
+// block kb+1; the final bf16 store of a tile overlaps the first K blocks of the next tile because the
+// running sums live in registers, not in TMEM.
+#pragma once
+#include "gemm_sm100.cuh"
+
+namespace dga {
+
+constexpr uint32_t kFp8Threads = 384;
+constexpr uint32_t kFp8BlockK = 128;   // elements == bytes == the scale granularity
+
+struct Fp8Params {
+    uint32_t m, n, k;
+    uint32_t block_n;
+    uint32_t num_stages;
+    uint32_t k_blocks;
+    uint32_t num_m_blocks, num_n_blocks;
+    uint32_t raster_group, raster_along_m;
+    uint32_t idesc;
+    uint32_t sfa_ld, sfb_ld;   // row pitch of the scale tensors, in floats
+    uint32_t sfb_rows;         // ceil(n / 128)
+    const float* sfa;          // [m, ceil(k/128)]
+    const float* sfb;          // [ceil(n/128), ceil(k/128)]
+};
+
+struct Fp8Smem {
+    uint32_t d_stage_bytes, a_stage_bytes, b_stage_bytes, off_d, off_a, off_b, off_bar, total;
+};
+__host__ __device__ inline Fp8Smem make_fp8_smem(uint32_t block_n, uint32_t cta, uint32_t stages) {
+    Fp8Smem l;
+    l.d_stage_bytes = kBlockM * kEpiCols * 2;   // bf16 staging chunk, 2 per warp group
+    l.a_stage_bytes = kBlockM * 128;
+    l.b_stage_bytes = (block_n / cta) * 128;
+    l.off_d = 0;
+    l.off_a = 4 * l.d_stage_bytes;
+    l.off_b = l.off_a + stages * l.a_stage_bytes;
+    l.off_bar = l.off_b + stages * l.b_stage_bytes;
+    l.total = l.off_bar + (2 * stages + 4) * 8 + 16;
+    return l;
+}
+
+__device__ __forceinline__ void stage_row_bf16(uint32_t stage_base, uint32_t row, const float (&v)[32]) {
+    const uint32_t row_base = stage_base + row * 64;
+    const uint32_t x = (row >> 1) & 3;
+#pragma unroll
+    for (uint32_t j = 0; j < 4; ++j) {
+        const uint32_t a = OutPack<__nv_bfloat16>::pack(v[8 * j + 0], v[8 * j + 1]);
+        const uint32_t b = OutPack<__nv_bfloat16>::pack(v[8 * j + 2], v[8 * j + 3]);
+        const uint32_t c = OutPack<__nv_bfloat16>::pack(v[8 * j + 4], v[8 * j + 5]);
+        const uint32_t d = OutPack<__nv_bfloat16>::pack(v[8 * j + 6], v[8 * j + 7]);
+        ptx::st_shared_v4(row_base + ((j ^ x) << 4), a, b, c, d);
+    }
+}
+
+template <int kCta, uint32_t kBN>
+__global__ void __launch_bounds__(kFp8Threads, 1)
+gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                      const __grid_constant__ CUtensorMap tm_d, const Fp8Params p) {
+    static_assert(kBN % 32 == 0 && kBN <= 256 && kBN % (16 * kCta) == 0, "unsupported block_n");
+    constexpr uint32_t kChunks = kBN / 32;
+    constexpr uint32_t kOwned = (kChunks + 1) / 2;   // chunks per warp group (group 1 may own one less)
+    constexpr uint32_t kTmemCols = (2 * kBN <= 32) ? 32 : (2 * kBN <= 64) ? 64 : (2 * kBN <= 128) ? 128
+                                   : (2 * kBN <= 256) ? 256 : 512;
+
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
+
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t cta_rank = (kCta == 2) ? ptx::cluster_ctarank() : 0u;
+    const bool is_leader = cta_rank == 0;
+    const uint32_t num_clusters = gridDim.x / kCta;
+    const uint32_t cluster_id = blockIdx.x / kCta;
+    const uint32_t num_tiles = p.num_m_blocks * p.num_n_blocks;
+    const uint32_t stages = p.num_stages;
+    const uint32_t k_blocks = p.k_blocks;
+
+    const Fp8Smem L = make_fp8_smem(kBN, kCta, stages);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.off_bar);
+    uint64_t* empty_bar = full_bar + stages;
+    uint64_t* part_full_bar = empty_bar + stages;    // [2] partial product of one K block is in TMEM
+    uint64_t* part_empty_bar = part_full_bar + 2;    // [2] promotion warps have read it
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(part_empty_bar + 2);
+
+    if constexpr (kCta == 2) ptx::cluster_sync();
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tensormap(&tm_a);
+        ptx::prefetch_tensormap(&tm_b);
+        ptx::prefetch_tensormap(&tm_d);
+    }
+    if (warp == 1 && lane == 0) {
+        for (uint32_t s = 0; s < stages; ++s) {
+            ptx::mbar_init(&full_bar[s], kCta);
+            ptx::mbar_init(&empty_bar[s], 1);
+        }
+        for (uint32_t s = 0; s < 2; ++s) {
+            ptx::mbar_init(&part_full_bar[s], 1);
+            ptx::mbar_init(&part_empty_bar[s], kCta * 8);   // one elected arrive per promotion warp of the pair
+        }
+        ptx::fence_mbar_init();
+    }
+    if (warp == 2) ptx::tmem_alloc<kCta>(tmem_ptr_smem, kTmemCols);
+    ptx::tc_fence_before();
+    if constexpr (kCta == 2) ptx::cluster_sync(); else __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+    constexpr uint32_t kLoadN = kBN / kCta;
+
+    if (warp < 4) {
+        ptx::setmaxnreg_dec<56>();
+        if (warp == 0) {
+            // ------------------------------------------------ TMA producer
+            uint32_t stage = 0, phase = 0;
+            for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters) {
+                uint32_t mb, nb;
+                tile_coords(p, t, mb, nb);
+                const int32_t m_idx = static_cast<int32_t>(mb * (kBlockM * kCta) + cta_rank * kBlockM);
+                const int32_t n_idx = static_cast<int32_t>(nb * kBN + cta_rank * kLoadN);
+                for (uint32_t kb = 0; kb < k_blocks; ++kb) {
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    if (ptx::elect_one()) {
+                        uint8_t* sa = smem + L.off_a + stage * L.a_stage_bytes;
+                        uint8_t* sb = smem + L.off_b + stage * L.b_stage_bytes;
+                        const int32_t k_idx = static_cast<int32_t>(kb * kFp8BlockK);
+                        if constexpr (kCta == 2) {
+                            ptx::tma_load_2d_pair(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
+                            ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
+                            if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * (L.a_stage_bytes + L.b_stage_bytes));
+                            else ptx::mbar_arrive_remote(&full_bar[stage], 0);
+                        } else {
+                            ptx::tma_load_2d(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
+                            ptx::tma_load_2d(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
+                            ptx::mbar_arrive_expect_tx(&full_bar[stage], L.a_stage_bytes + L.b_stage_bytes);
+                        }
+                    }
+                    __syncwarp();
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+            }
+        } else if (warp == 1 && is_leader) {
+            // -------------------------------------------------- MMA issuer
+            const uint32_t hi = static_cast<uint32_t>(make_smem_desc_hi(1024, kLayoutSw128) >> 32);
+            const uint32_t a_lo0 = ((smem_base + L.off_a) & 0x3FFFF) >> 4;
+            const uint32_t b_lo0 = ((smem_base + L.off_b) & 0x3FFFF) >> 4;
+            const uint32_t a_step = L.a_stage_bytes >> 4, b_step = L.b_stage_bytes >> 4;
+            const uint32_t idesc = p.idesc;
+            uint32_t stage = 0, phase = 0, pc = 0;   // pc: running K-block counter (selects the TMEM buffer)
+            for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters) {
+                for (uint32_t kb = 0; kb < k_blocks; ++kb, ++pc) {
+                    const uint32_t buf = pc & 1;
+                    ptx::mbar_wait(&part_empty_bar[buf], ((pc >> 1) & 1) ^ 1);
+                    ptx::mbar_wait(&full_bar[stage], phase);
+                    ptx::tc_fence_after();
+                    if (ptx::elect_one()) {
+                        const uint32_t a_lo = a_lo0 + stage * a_step;
+                        const uint32_t b_lo = b_lo0 + stage * b_step;
+                        const uint32_t tmem_d = tmem_base + buf * kBN;
+#pragma unroll
+                        for (uint32_t k = 0; k < 4; ++k) {   // 4 x (K = 32 fp8 = 32 bytes) inside the 128 B atom
+                            const uint64_t a_desc = (static_cast<uint64_t>(hi) << 32) | (a_lo + k * 2);
+                            const uint64_t b_desc = (static_cast<uint64_t>(hi) << 32) | (b_lo + k * 2);
+                            ptx::mma_f8<kCta>(tmem_d, a_desc, b_desc, idesc, k != 0);
+                        }
+                        ptx::mma_commit<kCta>(&empty_bar[stage]);
+                        ptx::mma_commit<kCta>(&part_full_bar[buf]);
+                    }
+                    __syncwarp();
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else {
+        // ------------------------------------------------ promotion + epilogue (warps 4..11)
+        ptx::setmaxnreg_inc<224>();
+        const uint32_t group = (warp - 4) >> 2;                  // warp group 0 / 1
+        const uint32_t quad = warp & 3;                          // TMEM lane quadrant this warp may read
+        const uint32_t row = quad * 32 + lane;                   // accumulator row inside the CTA tile
+        const uint32_t gtid = (threadIdx.x - 128) & 127;         // thread index inside the warp group (== row)
+        const uint32_t bar_id = 1 + group;
+        const uint32_t sbase0 = smem_base + L.off_d + group * 2 * L.d_stage_bytes;
+        uint8_t* sptr0 = smem + L.off_d + group * 2 * L.d_stage_bytes;
+        uint32_t pc = 0, sbuf = 0;
+        float acc[kOwned][32];
+
+        for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters) {
+            uint32_t mb, nb;
+            tile_coords(p, t, mb, nb);
+            const uint32_t m0 = mb * (kBlockM * kCta) + cta_rank * kBlockM;
+            const uint32_t n0 = nb * kBN;
+            const float* sfa_row = p.sfa + static_cast<uint64_t>(min(m0 + row, p.m - 1)) * p.sfa_ld;
+            // the tile's columns touch at most three 128-wide scale blocks
+            const uint32_t nblk0 = n0 >> 7;
+            const float* sfb0 = p.sfb + static_cast<uint64_t>(min(nblk0, p.sfb_rows - 1)) * p.sfb_ld;
+            const float* sfb1 = p.sfb + static_cast<uint64_t>(min(nblk0 + 1, p.sfb_rows - 1)) * p.sfb_ld;
+            const float* sfb2 = p.sfb + static_cast<uint64_t>(min(nblk0 + 2, p.sfb_rows - 1)) * p.sfb_ld;
+#pragma unroll
+            for (uint32_t ci = 0; ci < kOwned; ++ci)
+#pragma unroll
+                for (uint32_t j = 0; j < 32; ++j) acc[ci][j] = 0.f;
+
+            // scales are fetched two K blocks ahead (an L2 round trip is shorter than one block of MMAs)
+            float sa_c = __ldg(sfa_row), b0_c = __ldg(sfb0), b1_c = __ldg(sfb1), b2_c = __ldg(sfb2);
+            const uint32_t k1 = min(1u, k_blocks - 1);
+            float sa_n = __ldg(sfa_row + k1), b0_n = __ldg(sfb0 + k1), b1_n = __ldg(sfb1 + k1), b2_n = __ldg(sfb2 + k1);
+
+            for (uint32_t kb = 0; kb < k_blocks; ++kb, ++pc) {
+                const uint32_t k2 = min(kb + 2, k_blocks - 1);
+                const float sa_f = __ldg(sfa_row + k2), b0_f = __ldg(sfb0 + k2), b1_f = __ldg(sfb1 + k2),
+                            b2_f = __ldg(sfb2 + k2);
+                const uint32_t buf = pc & 1;
+                ptx::mbar_wait(&part_full_bar[buf], (pc >> 1) & 1);
+                ptx::tc_fence_after();
+                const uint32_t taddr = tmem_base + ((quad * 32) << 16) + buf * kBN;
+                uint32_t va[32], vb[32];
+                ptx::tmem_ld_32x32(taddr + group * 32, va);
+#pragma unroll
+                for (uint32_t ci = 0; ci < kOwned; ++ci) {
+                    const uint32_t c = group + 2 * ci;           // this group's ci-th chunk
+                    if (c < kChunks) {
+                        ptx::tmem_ld_wait();
+                        // next chunk's load flies while this chunk is folded in
+                        const bool more = (ci + 1 < kOwned) && (c + 2 < kChunks);
+                        if (more) {
+                            if (ci & 1) ptx::tmem_ld_32x32(taddr + (c + 2) * 32, va);
+                            else ptx::tmem_ld_32x32(taddr + (c + 2) * 32, vb);
+                        } else {
+                            // every chunk of this buffer is in registers: hand it back to the tensor core
+                            ptx::tc_fence_before();
+                            __syncwarp();
+                            if (ptx::elect_one()) {
+                                if constexpr (kCta == 2) ptx::mbar_arrive_remote(&part_empty_bar[buf], 0);
+                                else ptx::mbar_arrive(&part_empty_bar[buf]);
+                            }
+                        }
+                        const uint32_t which = ((n0 + c * 32) >> 7) - nblk0;
+                        const float s = sa_c * (which == 0 ? b0_c : which == 1 ? b1_c : b2_c);
+                        if (ci & 1) {
+#pragma unroll
+                            for (uint32_t j = 0; j < 32; ++j) acc[ci][j] = fmaf(__uint_as_float(vb[j]), s, acc[ci][j]);
+                        } else {
+#pragma unroll
+                            for (uint32_t j = 0; j < 32; ++j) acc[ci][j] = fmaf(__uint_as_float(va[j]), s, acc[ci][j]);
+                        }
+                    }
+                }
+                sa_c = sa_n; b0_c = b0_n; b1_c = b1_n; b2_c = b2_n;
+                sa_n = sa_f; b0_n = b0_f; b1_n = b1_f; b2_n = b2_f;
+            }
+
+            // ---- tile done: registers -> bf16 -> swizzled smem -> TMA store (per warp group)
+#pragma unroll
+            for (uint32_t ci = 0; ci < kOwned; ++ci) {
+                const uint32_t c = group + 2 * ci;
+                if (c < kChunks && n0 + c * 32 < p.n) {
+                    if (gtid == 0) ptx::tma_store_wait_read<1>();
+                    ptx::named_bar_sync(bar_id, 128);
+                    stage_row_bf16(sbase0 + sbuf * L.d_stage_bytes, row, acc[ci]);
+                    ptx::fence_async_smem();
+                    ptx::named_bar_sync(bar_id, 128);
+                    if (gtid == 0) {
+                        if (m0 < p.m)
+                            ptx::tma_store_2d(&tm_d, sptr0 + sbuf * L.d_stage_bytes,
+                                              static_cast<int32_t>(n0 + c * 32), static_cast<int32_t>(m0));
+                        ptx::tma_store_commit();
+                    }
+                    sbuf ^= 1;
+                }
+            }
+        }
+        if (gtid == 0) ptx::tma_store_wait_all<0>();
+    }
+
+    // ---------------------------------------------------------------- teardown
+    ptx::tc_fence_before();
+    if constexpr (kCta == 2) ptx::cluster_sync(); else __syncthreads();
+    if (warp == 2) ptx::tmem_dealloc<kCta>(tmem_base, kTmemCols);
+}
+
+}  // namespace dga

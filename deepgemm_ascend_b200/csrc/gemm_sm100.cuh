@@ -69,7 +69,8 @@ __host__ __device__ constexpr uint32_t make_idesc(uint32_t umma_m, uint32_t umma
 // one dimension so that the ~74 tiles in flight cover a compact rectangle and
 // share A/B panels in L2 (what DynamicGemmIdentityBlockSwizzle(offset,
 // direction) does for the reference, tiling_params.h:63-64).
-__device__ __forceinline__ void tile_coords(const GemmParams& p, uint32_t t, uint32_t& mb, uint32_t& nb) {
+template <typename P>
+__device__ __forceinline__ void tile_coords(const P& p, uint32_t t, uint32_t& mb, uint32_t& nb) {
     const uint32_t g = p.raster_group;
     if (p.raster_along_m) {
         // groups of g N-blocks; inside a group walk N fastest, then M

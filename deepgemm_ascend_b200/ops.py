@@ -142,3 +142,52 @@ def nshard_range(n, world_size, rank):
     b, c = ctypes.c_uint32(0), ctypes.c_uint32(0)
     check(lib.dgaNShardRange(n, world_size, rank, ctypes.byref(b), ctypes.byref(c)), "dgaNShardRange")
     return b.value, c.value
+
+
+# ---- fp8 e4m3 block-scaled (DeepGEMM semantics; not in the reference) -------------------------------------------
+def fp8_get_workspace_size(a, a_scale, mat2, w_scale, out):
+    ws = ctypes.c_uint64(0)
+    ex = ctypes.c_void_p(None)
+    d = [acl_tensor(t) for t in (a, a_scale, mat2, w_scale, out)]
+    check(lib.dgaFp8BlockScaledMatmulGetWorkspaceSize(*[ctypes.byref(x) for x in d], ctypes.byref(ws), ctypes.byref(ex)),
+          "dgaFp8BlockScaledMatmulGetWorkspaceSize")
+    return ws.value, ex
+
+
+def fp8_block_scaled_matmul(a, a_scale, weight, w_scale, out=None, stream=None):
+    """out[M,N] (bf16) = (a * a_scale) @ (weight * w_scale)^T.
+
+    a [M,K] float8_e4m3fn with a_scale [M, ceil(K/128)] fp32 (1x128 strips); weight [N,K] float8_e4m3fn with
+    w_scale [ceil(N/128), ceil(K/128)] fp32 (128x128 blocks)."""
+    _require_cuda(a, a_scale, weight, w_scale)
+    if out is None:
+        out = torch.empty((a.shape[0], weight.shape[0]), dtype=torch.bfloat16, device=a.device)
+    ws_bytes, ex = fp8_get_workspace_size(a, a_scale, weight.t(), w_scale, out)
+    check(lib.dgaFp8BlockScaledMatmul(None, ws_bytes, ex, _stream_ptr(stream)), "dgaFp8BlockScaledMatmul")
+    return out
+
+
+class Fp8Executor:
+    """Repeatable fp8 plan: phase 1 once, phase 2 per call."""
+
+    def __init__(self, a, a_scale, weight, w_scale, out):
+        _require_cuda(a, a_scale, weight, w_scale, out)
+        self._keep = (a, a_scale, weight, w_scale, out)
+        self.workspace_bytes, self._ex = fp8_get_workspace_size(a, a_scale, weight.t(), w_scale, out)
+        check(lib.dgaSetExecutorRepeatable(self._ex), "dgaSetExecutorRepeatable")
+
+    def __call__(self, stream=None):
+        check(lib.dgaFp8BlockScaledMatmul(None, self.workspace_bytes, self._ex, _stream_ptr(stream)),
+              "dgaFp8BlockScaledMatmul")
+        return self._keep[4]
+
+    def close(self):
+        if self._ex is not None:
+            destroy_executor(self._ex)
+            self._ex = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
