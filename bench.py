@@ -11,7 +11,8 @@ Workloads (BASELINE.json configs):
                      collective; the optional all-gather of C is timed separately and reported under "allgather")
   config5            bf16 M=16384 N=57344 K=7168, N-sharded over --gpus ranks (strong scaling) + all-gather of C
   m<M>               bf16 M in {1,16,...} at N=4096 K=7168 (dynamic-M sweep point; CUDA-graph of 20 launches per step)
-  fp8                e4m3 block-scaled M=4096 N=7168 K=16384
+  fp8                e4m3 block-scaled M=4096 N=7168 K=16384, UE8M0 (power-of-two) scales -> tensor-core block scaling
+  fp8_fp32scales     same shape, arbitrary fp32 scales -> software promotion kernel
 Timing: CUDA events on the launching stream, K timed steps after W >= 3 warm-ups, barrier + synchronize on both
 sides, max over ranks. Buffers rotate over enough distinct (A, B, C) sets to exceed 2x the 126 MB L2.
 The oracle (oracle/) is used only for the cpu_baseline leg and for --impl reference.
@@ -49,7 +50,7 @@ def workload_shape(name, world):
         return dict(m=4096, n=7168, k=2048, dtype="bf16", n_total=7168 * world, scaling="weak")
     if name == "config5":
         return dict(m=16384, n=57344 // world, k=7168, dtype="bf16", n_total=57344, scaling="strong")
-    if name == "fp8":
+    if name in ("fp8", "fp8_fp32scales"):
         return dict(m=4096, n=7168, k=16384, dtype="fp8", n_total=7168 * world, scaling="weak")
     if name.startswith("m") and name[1:].isdigit():
         return dict(m=int(name[1:]), n=4096, k=7168, dtype="bf16", n_total=4096 * world, scaling="weak")

@@ -37,8 +37,14 @@ def run_ours(args, rank, world):
             return x.to(torch.float8_e4m3fn)
         a_bufs = [quant(m) for _ in range(sets)]
         w_bufs = [quant(n) for _ in range(sets)]
-        sa = [torch.rand((m, -(-k // 128)), device=dev, generator=gen) + 0.5 for _ in range(sets)]
-        sw = [torch.rand((-(-n // 128), -(-k // 128)), device=dev, generator=gen) + 0.5 for _ in range(sets)]
+        def scales(rows):
+            if args.workload == "fp8_fp32scales":   # arbitrary fp32 scales: software promotion kernel
+                return torch.rand((rows, -(-k // 128)), device=dev, generator=gen) + 0.5
+            # UE8M0 (power-of-two) scales, DeepGEMM's format on Blackwell: tensor-core block scaling
+            e = torch.randint(-3, 4, (rows, -(-k // 128)), device=dev, generator=gen)
+            return torch.pow(2.0, e.float())
+        sa = [scales(m) for _ in range(sets)]
+        sw = [scales(-(-n // 128)) for _ in range(sets)]
         c_bufs = [torch.empty((m, n), device=dev, dtype=torch.bfloat16) for _ in range(sets)]
         execs = [dga.Fp8Executor(a_bufs[i], sa[i], w_bufs[i], sw[i], c_bufs[i]) for i in range(sets)]
     else:

@@ -47,9 +47,11 @@ static PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
     return fn;
 }
 
+constexpr int32_t kAclInt32 = 3;  // ACL_INT32: packed UE8M0 scale words
 static CUtensorMapDataType tmap_dtype(int32_t dtype) {
     switch (dtype) {
         case ACL_FLOAT: return CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+        case kAclInt32: return CU_TENSOR_MAP_DATA_TYPE_INT32;
         case ACL_FLOAT16: return CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
         case ACL_BF16: return CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
         default: return CU_TENSOR_MAP_DATA_TYPE_UINT8;
@@ -65,7 +67,7 @@ static int make_tmap_2d(CUtensorMap* map, const void* ptr, int32_t dtype, uint64
         set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver)");
         return ACLNN_ERR_RUNTIME_ERROR;
     }
-    const uint32_t eb = elem_bytes(dtype);
+    const uint32_t eb = dtype == kAclInt32 ? 4u : elem_bytes(dtype);
     cuuint64_t dims[2] = {inner, outer};
     cuuint64_t strides[1] = {ld * eb};
     cuuint32_t box[2] = {box_inner, box_outer};
@@ -124,7 +126,7 @@ static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaSt
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, gp));
+    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, L.tm_a, L.tm_b, gp));  // no scale maps here
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
 }
@@ -174,6 +176,7 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream) {
     gp.raster_along_m = p.swizzleDirection;
     gp.idesc = make_idesc(128 * cta, p.n1, p.dtype == ACL_BF16 ? 1u : 0u, 0, p.layoutTagB == 1 ? 0u : 1u);
     gp.b_stage_bytes = (p.n1 / cta) * 128;
+    gp.k_block_elems = 64;
     static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
     gp.debug = dbg;
     if (cta == 2)
@@ -259,9 +262,15 @@ struct Fp8Launch {
     uint64_t lda = 0, ldb = 0, ldd = 0, sfa_ld = 0, sfb_ld = 0;
     CUtensorMap tm_a, tm_b, tm_d;
     bool encoded = false;
+    // hardware block-scaled path (scales that are exact powers of two)
+    uint32_t mx_cta = 2, mx_bn = 224, mx_stages = 0, mx_grid = 0, mx_smem = 0, mx_chunks = 2;
+    uint64_t ws_sfa_off = 0, ws_sfb_off = 0, ws_flag_off = 0, ws_bytes = 0;
+    CUtensorMap tm_b_mx, tm_sfa, tm_sfb;
+    const void* encoded_ws = nullptr;
 };
 
 static const uint32_t kFp8TilesPair[] = {256, 224, 192, 128};
+static const uint32_t kMxTilesPair[] = {224, 192, 128};   // 2 accumulator stages + scale columns must fit 512 TMEM columns
 
 // Wave-balanced tile for the fp8 kernel: fewest (waves x block_n) column-units, ties to the wider tile.
 static void plan_fp8(Fp8Launch& L) {
@@ -284,6 +293,82 @@ static void plan_fp8(Fp8Launch& L) {
     const uint32_t tiles = ceil_div(L.m, 128 * L.cta) * ceil_div(L.n, L.bn);
     L.grid = std::min(tiles, hw.smCount / L.cta) * L.cta;
     L.smem = make_fp8_smem(L.bn, L.cta, L.stages).total + 1024;
+
+    // block-scaled plan
+    if (L.m <= 128) {
+        L.mx_cta = 1; L.mx_bn = 128;
+    } else {
+        L.mx_cta = 2;
+        uint64_t best = ~0ull;
+        for (uint32_t bn : kMxTilesPair) {
+            const uint64_t tiles_bn = uint64_t(ceil_div(L.m, 256)) * ceil_div(L.n, bn);
+            const uint64_t waves = (tiles_bn + hw.smCount / 2 - 1) / (hw.smCount / 2);
+            const uint64_t cost = waves * bn;
+            if (cost < best) { best = cost; L.mx_bn = bn; }
+        }
+    }
+    L.mx_chunks = ceil_div(L.mx_bn, 128);
+    const uint32_t sf_stage = 512 * (1 + L.mx_chunks);
+    const uint32_t mx_per_stage = 128 * 128 + (L.mx_bn / L.mx_cta) * 128 + sf_stage;
+    const uint32_t mx_fixed = 2 * 128 * 32 * 2 + 1024 + 256;
+    L.mx_stages = std::min<uint32_t>(10, (hw.smemBytes - mx_fixed) / mx_per_stage);
+    const uint32_t mx_tiles = ceil_div(L.m, 128 * L.mx_cta) * ceil_div(L.n, L.mx_bn);
+    L.mx_grid = std::min(mx_tiles, hw.smCount / L.mx_cta) * L.mx_cta;
+    L.mx_smem = make_smem_layout(2, (L.mx_bn / L.mx_cta) * 128, L.mx_stages, sf_stage).total + 1024;
+    // workspace: packed A scales [K/512][ceil(M/128)][128] words, packed B scales [K/512][n tiles][chunks][128], flag
+    const uint64_t kg = ceil_div(L.k, 512);
+    L.ws_sfa_off = 0;
+    L.ws_sfb_off = kg * ceil_div(L.m, 128) * 512;
+    L.ws_flag_off = L.ws_sfb_off + kg * ceil_div(L.n, L.mx_bn) * L.mx_chunks * 512;
+    L.ws_bytes = L.ws_flag_off + 256;
+}
+
+// Packs fp32 scales into the UE8M0 words the block-scaled MMA reads: word = exponent bytes of 4 consecutive K
+// blocks; inside every 128-entry chunk entry (r*32 + l) is stored at l*4 + r, the 32-row x 128-bit order
+// tcgen05.cp.32x128b.warpx4 expects.  Sets *flag when any scale is not an exact power of two (then the
+// promotion kernel, not the block-scaled one, must produce the result).
+__global__ void fp8_pack_scales_kernel(const float* __restrict__ sfa, const float* __restrict__ sfb, uint32_t m,
+                                       uint32_t n, uint32_t kb_total, uint32_t sfa_ld, uint32_t sfb_ld,
+                                       uint32_t bn, uint32_t chunks, uint32_t* __restrict__ out_a,
+                                       uint32_t* __restrict__ out_b, int32_t* __restrict__ flag) {
+    const uint32_t m_chunks = (m + 127) / 128, n_tiles = (n + bn - 1) / bn, kgs = (kb_total + 3) / 4;
+    const uint64_t total_a = uint64_t(kgs) * m_chunks * 128, total_b = uint64_t(kgs) * n_tiles * chunks * 128;
+    bool bad = false;
+    for (uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; i < total_a + total_b;
+         i += uint64_t(gridDim.x) * blockDim.x) {
+        const bool is_a = i < total_a;
+        const uint64_t j = is_a ? i : i - total_a;
+        const uint32_t pos = uint32_t(j & 127), l = pos >> 2, r = pos & 3, e = r * 32 + l;   // e: entry inside the chunk
+        const uint64_t chunk = j >> 7;
+        const float* src = nullptr;
+        uint32_t kg;
+        if (is_a) {
+            kg = uint32_t(chunk / m_chunks);
+            const uint32_t row = uint32_t(chunk % m_chunks) * 128 + e;
+            if (row < m) src = sfa + uint64_t(row) * sfa_ld;
+        } else {
+            const uint32_t c = uint32_t(chunk % chunks);
+            const uint64_t t = chunk / chunks;
+            kg = uint32_t(t / n_tiles);
+            const uint32_t in_tile = c * 128 + e;
+            const uint32_t col = uint32_t(t % n_tiles) * bn + in_tile;
+            if (in_tile < bn && col < n) src = sfb + uint64_t(col >> 7) * sfb_ld;
+        }
+        uint32_t word = 0x7F7F7F7Fu;   // 2^0 everywhere
+        if (src != nullptr) {
+            word = 0;
+            for (uint32_t b = 0; b < 4; ++b) {
+                const uint32_t kb = kg * 4 + b;
+                uint32_t bits = 0x3F800000u;
+                if (kb < kb_total) bits = __float_as_uint(__ldg(src + kb));
+                const uint32_t ex = (bits >> 23) & 0xFF;
+                if ((bits & 0x807FFFFFu) != 0 || ex == 0 || ex == 255) bad = true;
+                word |= ex << (8 * b);
+            }
+        }
+        (is_a ? out_a : out_b)[j] = word;
+    }
+    if (bad) atomicOr(flag, 1);
 }
 
 template <int kCta, uint32_t kBN>
@@ -308,21 +393,93 @@ static int launch_fp8_inst(const Fp8Launch& L, const Fp8Params& fp, cudaStream_t
     return ACLNN_SUCCESS;
 }
 
-static int launch_fp8(Fp8Launch& L, cudaStream_t stream) {
+template <int kCta>
+static int launch_mx_inst(const Fp8Launch& L, const GemmParams& gp, cudaStream_t stream) {
+    auto kernel = gemm_sm100_kernel<kCta, __nv_bfloat16, false, true>;
+    int rc = set_smem_attr(kernel, L.mx_smem);
+    if (rc != ACLNN_SUCCESS) return rc;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(L.mx_grid);
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.dynamicSmemBytes = L.mx_smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kCta;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b_mx, L.tm_d, L.tm_sfa, L.tm_sfb, gp));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return ACLNN_SUCCESS;
+}
+
+// mode: 0 = decide on the device from the scale values (both kernels are enqueued, the gate flag lets exactly one
+// run), 1 = promotion kernel only, 2 = block-scaled kernel only (caller guarantees power-of-two scales).
+static int launch_fp8(Fp8Launch& L, void* workspace, cudaStream_t stream) {
+    static const int mode = [] { const char* e = std::getenv("DGA_FP8_MODE"); return e ? std::atoi(e) : 0; }();
     if (!L.encoded) {
         int rc = make_tmap_2d(&L.tm_a, L.a, ACL_FLOAT8_E4M3FN, L.k, L.m, L.lda, 128, 128, CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc != ACLNN_SUCCESS) return rc;
         rc = make_tmap_2d(&L.tm_b, L.b, ACL_FLOAT8_E4M3FN, L.k, L.n, L.ldb, 128, L.bn / L.cta, CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc != ACLNN_SUCCESS) return rc;
+        rc = make_tmap_2d(&L.tm_b_mx, L.b, ACL_FLOAT8_E4M3FN, L.k, L.n, L.ldb, 128, L.mx_bn / L.mx_cta,
+                          CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc != ACLNN_SUCCESS) return rc;
         rc = make_tmap_2d(&L.tm_d, L.d, ACL_BF16, L.n, L.m, L.ldd, 32, 128, CU_TENSOR_MAP_SWIZZLE_64B);
         if (rc != ACLNN_SUCCESS) return rc;
         L.encoded = true;
+    }
+    char* ws = static_cast<char*>(workspace);
+    const uint32_t kb_total = ceil_div(L.k, 128), kgs = ceil_div(L.k, 512);
+    const uint32_t m_chunks = ceil_div(L.m, 128), n_tiles = ceil_div(L.n, L.mx_bn);
+    if (mode != 1 && L.encoded_ws != workspace) {
+        int rc = make_tmap_2d(&L.tm_sfa, ws + L.ws_sfa_off, kAclInt32, 128, uint64_t(kgs) * m_chunks, 128, 128, 1,
+                              CU_TENSOR_MAP_SWIZZLE_NONE);
+        if (rc != ACLNN_SUCCESS) return rc;
+        rc = make_tmap_2d(&L.tm_sfb, ws + L.ws_sfb_off, kAclInt32, 128, uint64_t(kgs) * n_tiles * L.mx_chunks, 128, 128,
+                          L.mx_chunks, CU_TENSOR_MAP_SWIZZLE_NONE);
+        if (rc != ACLNN_SUCCESS) return rc;
+        L.encoded_ws = workspace;
+    }
+    int32_t* flag = reinterpret_cast<int32_t*>(ws + L.ws_flag_off);
+    if (mode != 1) {
+        DGA_CUDA(cudaMemsetAsync(flag, 0, sizeof(int32_t), stream));
+        const uint64_t words = uint64_t(kgs) * (uint64_t(m_chunks) + uint64_t(n_tiles) * L.mx_chunks) * 128;
+        const uint32_t blocks = uint32_t(std::min<uint64_t>((words + 255) / 256, 148 * 8));
+        fp8_pack_scales_kernel<<<blocks, 256, 0, stream>>>(L.sfa, L.sfb, L.m, L.n, kb_total, uint32_t(L.sfa_ld),
+                                                           uint32_t(L.sfb_ld), L.mx_bn, L.mx_chunks,
+                                                           reinterpret_cast<uint32_t*>(ws + L.ws_sfa_off),
+                                                           reinterpret_cast<uint32_t*>(ws + L.ws_sfb_off), flag);
+        DGA_CUDA(cudaGetLastError());
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        GemmParams gp{};
+        gp.m = L.m; gp.n = L.n; gp.k = L.k;
+        gp.block_n = L.mx_bn;
+        gp.num_stages = L.mx_stages;
+        gp.k_blocks = kb_total;
+        gp.num_m_blocks = ceil_div(L.m, 128 * L.mx_cta);
+        gp.num_n_blocks = n_tiles;
+        gp.raster_group = 8;
+        gp.raster_along_m = L.m > L.n ? 0 : 1;
+        // block-scaled instruction descriptor: e4m3 x e4m3, UE8M0 scales (bit 23), N >> 3 at [17,23), M >> 4 at [24,29)
+        gp.idesc = (1u << 23) | ((L.mx_bn >> 3) << 17) | (((128u * L.mx_cta) >> 4) << 24);
+        gp.b_stage_bytes = (L.mx_bn / L.mx_cta) * 128;
+        gp.k_block_elems = 128;
+        gp.sf_n_chunks = L.mx_chunks;
+        gp.sf_m_chunks = m_chunks;
+        gp.gate = mode == 0 ? flag : nullptr;
+        gp.gate_expect = 0;
+        int rc = L.mx_cta == 2 ? launch_mx_inst<2>(L, gp, stream) : launch_mx_inst<1>(L, gp, stream);
+        if (rc != ACLNN_SUCCESS) return rc;
+        if (mode == 2) return ACLNN_SUCCESS;
     }
     Fp8Params fp{};
     fp.m = L.m; fp.n = L.n; fp.k = L.k;
     fp.block_n = L.bn;
     fp.num_stages = L.stages;
-    fp.k_blocks = ceil_div(L.k, 128);
+    fp.k_blocks = kb_total;
     fp.num_m_blocks = ceil_div(L.m, 128 * L.cta);
     fp.num_n_blocks = ceil_div(L.n, L.bn);
     fp.raster_group = 8;
@@ -331,6 +488,8 @@ static int launch_fp8(Fp8Launch& L, cudaStream_t stream) {
     fp.sfa_ld = uint32_t(L.sfa_ld); fp.sfb_ld = uint32_t(L.sfb_ld);
     fp.sfb_rows = ceil_div(L.n, 128);
     fp.sfa = L.sfa; fp.sfb = L.sfb;
+    fp.gate = mode == 0 ? flag : nullptr;
+    fp.gate_expect = 1;
     if (L.cta == 1) return launch_fp8_inst<1, 128>(L, fp, stream);
     switch (L.bn) {
         case 256: return launch_fp8_inst<2, 256>(L, fp, stream);
@@ -577,16 +736,24 @@ aclnnStatus dgaFp8BlockScaledMatmulGetWorkspaceSize(const aclTensor* self, const
         return ACLNN_ERR_INNER_TILING_ERROR;
     }
     plan_fp8(L);
-    *workspaceSize = 0;
+    *workspaceSize = L.ws_bytes;
     *executor = ex;
     return ACLNN_SUCCESS;
 }
-aclnnStatus dgaFp8BlockScaledMatmul(void*, uint64_t, aclOpExecutor* executor, aclrtStream stream) {
+aclnnStatus dgaFp8BlockScaledMatmul(void* workspace, uint64_t workspaceSize, aclOpExecutor* executor,
+                                    aclrtStream stream) {
     if (executor == nullptr || !executor->is_fp8) {
         set_error("not an fp8 executor");
         return ACLNN_ERR_PARAM_NULLPTR;
     }
-    aclnnStatus rc = launch_fp8(executor->fp8, static_cast<cudaStream_t>(stream));
+    aclnnStatus rc;
+    if (workspace == nullptr || workspaceSize < executor->fp8.ws_bytes ||
+        (reinterpret_cast<uintptr_t>(workspace) & 127) != 0) {
+        set_error("fp8 matmul needs the workspace phase 1 asked for (128-byte aligned)");
+        rc = ACLNN_ERR_PARAM_INVALID;
+    } else {
+        rc = launch_fp8(executor->fp8, workspace, static_cast<cudaStream_t>(stream));
+    }
     if (!executor->repeatable) delete executor;
     return rc;
 }

@@ -33,6 +33,8 @@ struct Fp8Params {
     uint32_t sfb_rows;         // ceil(n / 128)
     const float* sfa;          // [m, ceil(k/128)]
     const float* sfb;          // [ceil(n/128), ceil(k/128)]
+    const int32_t* gate;       // run only when *gate == gate_expect (nullptr: always)
+    int32_t gate_expect;
 };
 
 struct Fp8Smem {
@@ -69,6 +71,7 @@ __global__ void __launch_bounds__(kFp8Threads, 1)
 gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                       const __grid_constant__ CUtensorMap tm_d, const Fp8Params p) {
     static_assert(kBN % 32 == 0 && kBN <= 256 && kBN % (16 * kCta) == 0, "unsupported block_n");
+    if (p.gate != nullptr && *p.gate != p.gate_expect) return;   // grid-uniform
     constexpr uint32_t kChunks = kBN / 32;
     constexpr uint32_t kOwned = (kChunks + 1) / 2;   // chunks per warp group (group 1 may own one less)
     constexpr uint32_t kTmemCols = (2 * kBN <= 32) ? 32 : (2 * kBN <= 64) ? 64 : (2 * kBN <= 128) ? 128

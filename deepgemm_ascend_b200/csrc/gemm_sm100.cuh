@@ -45,6 +45,12 @@ struct GemmParams {
     uint32_t idesc;          // tcgen05 instruction descriptor
     uint32_t b_stage_bytes;  // bytes of B per CTA per stage
     uint32_t debug;          // bottleneck isolation (DGA_DEBUG_FLAGS): 1 no TMA loads, 2 no MMAs, 4 no stores
+    uint32_t k_block_elems;  // elements per 128-byte K block: 64 (16-bit) or 128 (fp8)
+    // kMx (hardware block-scaled fp8) only:
+    uint32_t sf_n_chunks;    // 128-column scale chunks per N tile
+    uint32_t sf_m_chunks;    // ceil(m / 128)
+    const int32_t* gate;     // device flag; the kernel runs only when *gate == gate_expect (nullptr: always)
+    int32_t gate_expect;
 };
 
 // --- descriptors -----------------------------------------------------------
@@ -132,10 +138,11 @@ __device__ __forceinline__ void stage_row(uint32_t stage_base, uint32_t row, con
 // Shared-memory carve-up (offsets from a 1024-aligned base; identical in both
 // CTAs of a pair, which cta_group::2 descriptors rely on).
 struct SmemLayout {
-    uint32_t d_stage_bytes, a_stage_bytes, b_stage_bytes;
-    uint32_t off_d, off_a, off_b, off_bar, total;
+    uint32_t d_stage_bytes, a_stage_bytes, b_stage_bytes, sf_stage_bytes;
+    uint32_t off_d, off_a, off_b, off_sf, off_bar, total;
 };
-__host__ __device__ inline SmemLayout make_smem_layout(uint32_t out_elem_bytes, uint32_t b_stage_bytes, uint32_t stages) {
+__host__ __device__ inline SmemLayout make_smem_layout(uint32_t out_elem_bytes, uint32_t b_stage_bytes, uint32_t stages,
+                                                       uint32_t sf_stage_bytes = 0) {
     SmemLayout l;
     l.d_stage_bytes = kBlockM * kEpiCols * out_elem_bytes;
     l.a_stage_bytes = kBlockM * kBlockKBytes;
@@ -143,16 +150,25 @@ __host__ __device__ inline SmemLayout make_smem_layout(uint32_t out_elem_bytes, 
     l.off_d = 0;
     l.off_a = 2 * l.d_stage_bytes;
     l.off_b = l.off_a + stages * l.a_stage_bytes;
-    l.off_bar = l.off_b + stages * l.b_stage_bytes;
+    l.sf_stage_bytes = sf_stage_bytes;   // per stage: 512 B of A scales + 512 B per 128 columns of B scales
+    l.off_sf = l.off_b + stages * l.b_stage_bytes;
+    l.off_bar = l.off_sf + stages * sf_stage_bytes;
     // full[stages] empty[stages] tmem_full[2] tmem_empty[2] + tmem ptr
     l.total = l.off_bar + (2 * stages + 4) * 8 + 16;
     return l;
 }
 
-template <int kCta, typename OutT, bool kBMn>
+// kMx: e4m3 operands with UE8M0 block scales applied by the tensor core (kind::mxf8f6f4.block_scale).  The
+// scale words arrive pre-packed (4 consecutive 128-wide K blocks per 32-bit word, already in the 32x128-bit
+// order tcgen05.cp wants) from the workspace, one TMA box per 4 K blocks, and live in TMEM behind the two
+// accumulator stages.
+template <int kCta, typename OutT, bool kBMn, bool kMx = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
-                  const __grid_constant__ CUtensorMap tm_d, const GemmParams p) {
+                  const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_sfa,
+                  const __grid_constant__ CUtensorMap tm_sfb, const GemmParams p) {
+    static_assert(!(kMx && kBMn), "block-scaled fp8 wants K-major operands");
+    if (p.gate != nullptr && *p.gate != p.gate_expect) return;   // grid-uniform
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
@@ -166,7 +182,8 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     const uint32_t num_tiles = p.num_m_blocks * p.num_n_blocks;
     const uint32_t stages = p.num_stages;
 
-    const SmemLayout L = make_smem_layout(sizeof(OutT), p.b_stage_bytes, stages);
+    const uint32_t sf_stage_bytes = kMx ? 512u * (1u + p.sf_n_chunks) : 0u;
+    const SmemLayout L = make_smem_layout(sizeof(OutT), p.b_stage_bytes, stages, sf_stage_bytes);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.off_bar);
     uint64_t* empty_bar = full_bar + stages;
     uint64_t* tmem_full_bar = empty_bar + stages;
@@ -179,6 +196,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         ptx::prefetch_tensormap(&tm_a);
         ptx::prefetch_tensormap(&tm_b);
         ptx::prefetch_tensormap(&tm_d);
+        if constexpr (kMx) {
+            ptx::prefetch_tensormap(&tm_sfa);
+            ptx::prefetch_tensormap(&tm_sfb);
+        }
     }
     if (warp == 1 && lane == 0) {
         for (uint32_t s = 0; s < stages; ++s) {
@@ -219,7 +240,26 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                 } else if (ptx::elect_one()) {
                     uint8_t* sa = smem + L.off_a + stage * L.a_stage_bytes;
                     uint8_t* sb = smem + L.off_b + stage * L.b_stage_bytes;
-                    const int32_t k_idx = static_cast<int32_t>(kb * 64);
+                    const int32_t k_idx = static_cast<int32_t>(kb * p.k_block_elems);
+                    uint32_t sf_bytes = 0;
+                    if constexpr (kMx) {
+                        if ((kb & 3) == 0) {   // one scale word covers 4 K blocks
+                            uint8_t* ssf = smem + L.off_sf + stage * L.sf_stage_bytes;
+                            const int32_t kg = static_cast<int32_t>(kb >> 2);
+                            const int32_t row_a = kg * static_cast<int32_t>(p.sf_m_chunks) +
+                                                  static_cast<int32_t>(mb * kCta + cta_rank);
+                            const int32_t row_b = (kg * static_cast<int32_t>(p.num_n_blocks) + static_cast<int32_t>(nb)) *
+                                                  static_cast<int32_t>(p.sf_n_chunks);
+                            if constexpr (kCta == 2) {
+                                ptx::tma_load_2d_pair(&tm_sfa, &full_bar[stage], ssf, 0, row_a);
+                                ptx::tma_load_2d_pair(&tm_sfb, &full_bar[stage], ssf + 512, 0, row_b);
+                            } else {
+                                ptx::tma_load_2d(&tm_sfa, &full_bar[stage], ssf, 0, row_a);
+                                ptx::tma_load_2d(&tm_sfb, &full_bar[stage], ssf + 512, 0, row_b);
+                            }
+                            sf_bytes = L.sf_stage_bytes;
+                        }
+                    }
                     if constexpr (kCta == 2) {
                         ptx::tma_load_2d_pair(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
                         if constexpr (kBMn) {
@@ -228,7 +268,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                         } else {
                             ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
                         }
-                        if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * (L.a_stage_bytes + L.b_stage_bytes));
+                        if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * (L.a_stage_bytes + L.b_stage_bytes + sf_bytes));
                         else ptx::mbar_arrive_remote(&full_bar[stage], 0);
                     } else {
                         ptx::tma_load_2d(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
@@ -238,7 +278,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                         } else {
                             ptx::tma_load_2d(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
                         }
-                        ptx::mbar_arrive_expect_tx(&full_bar[stage], L.a_stage_bytes + L.b_stage_bytes);
+                        ptx::mbar_arrive_expect_tx(&full_bar[stage], L.a_stage_bytes + L.b_stage_bytes + sf_bytes);
                     }
                 }
                 __syncwarp();
@@ -261,6 +301,8 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
             constexpr uint32_t kBStepLo = kBMn ? (16 * 128) >> 4 : 32 >> 4;  // one UMMA_K (16 elements) along K
             const uint32_t idesc = p.idesc;
             const uint32_t k_blocks = p.k_blocks;
+            const uint32_t tmem_sfa = tmem_base + 2 * p.block_n;   // 4 columns; B scales follow
+            const uint32_t tmem_sfb = tmem_sfa + 4;
             uint32_t stage = 0, phase = 0, iter = 0;
             for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters, ++iter) {
                 const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
@@ -273,11 +315,27 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                     if (ptx::elect_one()) {
                         const uint32_t a_lo = a_lo0 + stage * a_step;
                         const uint32_t b_lo = b_lo0 + stage * b_step;
+                        uint32_t idesc_k = idesc;
+                        if constexpr (kMx) {
+                            if ((kb & 3) == 0) {
+                                // scale words of the next 4 K blocks: smem -> TMEM (ordered with the MMAs in the tensor pipe)
+                                const uint64_t sf_hi = make_smem_desc_hi(128, 0);
+                                const uint32_t sf_lo = ((smem_base + L.off_sf + stage * L.sf_stage_bytes) & 0x3FFFF) >> 4;
+                                ptx::tmem_cp_32x128b_warpx4<kCta>(tmem_sfa, sf_hi | sf_lo);
+                                for (uint32_t i = 0; i < p.sf_n_chunks; ++i)
+                                    ptx::tmem_cp_32x128b_warpx4<kCta>(tmem_sfb + 4 * i, sf_hi | (sf_lo + 32 * (1 + i)));
+                            }
+                            const uint32_t sf_id = kb & 3;
+                            idesc_k = idesc | (sf_id << 29) | (sf_id << 4);
+                        }
 #pragma unroll
                         for (uint32_t k = 0; k < 4; ++k) {
                             const uint64_t a_desc = (static_cast<uint64_t>(a_hi) << 32) | (a_lo + k * 2);
                             const uint64_t b_desc = (static_cast<uint64_t>(b_hi) << 32) | (b_lo + k * kBStepLo);
-                            if (!(p.debug & 2)) ptx::mma_f16<kCta>(tmem_d, a_desc, b_desc, idesc, (kb | k) != 0);
+                            if constexpr (kMx)
+                                ptx::mma_mxf8<kCta>(tmem_d, a_desc, b_desc, idesc_k, tmem_sfa, tmem_sfb, (kb | k) != 0);
+                            else if (!(p.debug & 2))
+                                ptx::mma_f16<kCta>(tmem_d, a_desc, b_desc, idesc_k, (kb | k) != 0);
                         }
                         ptx::mma_commit<kCta>(&empty_bar[stage]);
                         if (kb + 1 == k_blocks) ptx::mma_commit<kCta>(&tmem_full_bar[as]);

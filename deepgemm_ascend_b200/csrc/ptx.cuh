@@ -247,6 +247,35 @@ __device__ __forceinline__ void mma_f8(uint32_t tmem_d, uint64_t desc_a, uint64_
     }
 }
 
+// Block-scaled e4m3 x e4m3 -> fp32: UE8M0 scale factors for A rows / B columns sit in TMEM (tcgen05.cp below),
+// one scale per 32 K elements (scale_vec::1X); the sf ids in idesc pick the byte of the 32-bit scale word.
+template <int kCtaGroup>
+__device__ __forceinline__ void mma_mxf8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                         uint32_t tmem_sfa, uint32_t tmem_sfb, uint32_t accumulate) {
+    if constexpr (kCtaGroup == 1) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::mxf8f6f4.block_scale [%0], %1, %2, %3, [%5], [%6], p;\n\t}\n"
+            :: "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(tmem_sfa), "r"(tmem_sfb)
+            : "memory");
+    } else {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::mxf8f6f4.block_scale [%0], %1, %2, %3, [%5], [%6], p;\n\t}\n"
+            :: "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(tmem_sfa), "r"(tmem_sfb)
+            : "memory");
+    }
+}
+// smem -> TMEM copy of 32 rows x 128 bits, broadcast to the four 32-lane quadrants (scale-factor layout).
+// cta_group::2: both CTAs of the pair copy from their own shared memory at the same offset.
+template <int kCtaGroup>
+__device__ __forceinline__ void tmem_cp_32x128b_warpx4(uint32_t taddr, uint64_t smem_desc) {
+    if constexpr (kCtaGroup == 1)
+        asm volatile("tcgen05.cp.cta_group::1.32x128b.warpx4 [%0], %1;" :: "r"(taddr), "l"(smem_desc) : "memory");
+    else
+        asm volatile("tcgen05.cp.cta_group::2.32x128b.warpx4 [%0], %1;" :: "r"(taddr), "l"(smem_desc) : "memory");
+}
+
 // All previously issued MMAs of this thread done -> one arrival on `bar`.
 // cta_group::2: arrival is multicast to the same barrier in both CTAs.
 template <int kCtaGroup>

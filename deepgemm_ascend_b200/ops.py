@@ -163,7 +163,9 @@ def fp8_block_scaled_matmul(a, a_scale, weight, w_scale, out=None, stream=None):
     if out is None:
         out = torch.empty((a.shape[0], weight.shape[0]), dtype=torch.bfloat16, device=a.device)
     ws_bytes, ex = fp8_get_workspace_size(a, a_scale, weight.t(), w_scale, out)
-    check(lib.dgaFp8BlockScaledMatmul(None, ws_bytes, ex, _stream_ptr(stream)), "dgaFp8BlockScaledMatmul")
+    ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=a.device)
+    check(lib.dgaFp8BlockScaledMatmul(ctypes.c_void_p(ws.data_ptr()), ws_bytes, ex, _stream_ptr(stream)),
+          "dgaFp8BlockScaledMatmul")
     return out
 
 
@@ -175,10 +177,11 @@ class Fp8Executor:
         self._keep = (a, a_scale, weight, w_scale, out)
         self.workspace_bytes, self._ex = fp8_get_workspace_size(a, a_scale, weight.t(), w_scale, out)
         check(lib.dgaSetExecutorRepeatable(self._ex), "dgaSetExecutorRepeatable")
+        self._ws = torch.empty(max(self.workspace_bytes, 1), dtype=torch.uint8, device=out.device)
 
     def __call__(self, stream=None):
-        check(lib.dgaFp8BlockScaledMatmul(None, self.workspace_bytes, self._ex, _stream_ptr(stream)),
-              "dgaFp8BlockScaledMatmul")
+        check(lib.dgaFp8BlockScaledMatmul(ctypes.c_void_p(self._ws.data_ptr()), self.workspace_bytes, self._ex,
+                                          _stream_ptr(stream)), "dgaFp8BlockScaledMatmul")
         return self._keep[4]
 
     def close(self):

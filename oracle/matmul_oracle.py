@@ -151,7 +151,15 @@ def from_e4m3_bits(bits):
     return E4M3_VALUES[np.asarray(bits, dtype=np.uint8)]
 
 
-def per_token_cast_to_fp8(x):
+def ceil_to_ue8m0(sf):
+    """Round a positive fp32 scale up to the next power of two (upstream deep_gemm/utils/math.py ceil_to_ue8m0):
+    the scale format Blackwell's block-scaled MMA consumes."""
+    bits = np.asarray(sf, dtype=np.float32).view(np.uint32)
+    exp = ((bits >> np.uint32(23)) & np.uint32(0xFF)) + ((bits & np.uint32(0x7FFFFF)) != 0).astype(np.uint32)
+    return (np.clip(exp, 1, 254).astype(np.uint32) << np.uint32(23)).view(np.float32)
+
+
+def per_token_cast_to_fp8(x, use_ue8m0=False):
     """1x128 activation scaling (upstream deep_gemm/utils/math.py:25-37): per row and 128-column strip,
     scale = max(|x|, 1e-4) / 448; codes = e4m3(x / scale). Returns (codes uint8 [m,k], scales fp32 [m, ceil(k/128)])."""
     x = np.asarray(x, dtype=np.float32)
@@ -162,11 +170,13 @@ def per_token_cast_to_fp8(x):
     v = xp.reshape(m, kp // 128, 128)
     amax = np.maximum(np.abs(v).max(axis=2), 1e-4).astype(np.float32)
     sf = (amax / np.float32(448.0)).astype(np.float32)
+    if use_ue8m0:
+        sf = ceil_to_ue8m0(sf)
     codes = to_e4m3_bits(v * (np.float32(1.0) / sf)[:, :, None]).reshape(m, kp)[:, :k]
     return np.ascontiguousarray(codes), sf
 
 
-def per_block_cast_to_fp8(w):
+def per_block_cast_to_fp8(w, use_ue8m0=False):
     """128x128 weight scaling (upstream deep_gemm/utils/math.py:50-60). w is [n, k].
     Returns (codes uint8 [n,k], scales fp32 [ceil(n/128), ceil(k/128)])."""
     w = np.asarray(w, dtype=np.float32)
@@ -177,6 +187,8 @@ def per_block_cast_to_fp8(w):
     v = wp.reshape(npad // 128, 128, kpad // 128, 128)
     amax = np.maximum(np.abs(v).max(axis=(1, 3)), 1e-4).astype(np.float32)
     sf = (amax / np.float32(448.0)).astype(np.float32)
+    if use_ue8m0:
+        sf = ceil_to_ue8m0(sf)
     codes = to_e4m3_bits(v * (np.float32(1.0) / sf)[:, None, :, None]).reshape(npad, kpad)[:n, :k]
     return np.ascontiguousarray(codes), sf
 

