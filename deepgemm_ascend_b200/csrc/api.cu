@@ -157,7 +157,7 @@ static int encode_common(DenseLaunch& L) {
                         wide ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B);
 }
 
-static int launch_common(DenseLaunch& L, cudaStream_t stream) {
+static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     const DgaTilingPlan& p = L.plan;
     if (!L.encoded) {
         int rc = encode_common(L);
@@ -177,6 +177,29 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream) {
     gp.idesc = make_idesc(128 * cta, p.n1, p.dtype == ACL_BF16 ? 1u : 0u, 0, p.layoutTagB == 1 ? 0u : 1u);
     gp.b_stage_bytes = (p.n1 / cta) * 128;
     gp.k_block_elems = 64;
+    gp.dp_tiles = gp.num_m_blocks * gp.num_n_blocks;
+    gp.sk_tiles = 0;
+    if (p.kernelSerial == DGA_KERNEL_STREAMK) {
+        const uint32_t clusters = p.blockDim / cta;
+        streamk_split(gp.num_m_blocks * gp.num_n_blocks, clusters, gp.k_blocks, gp.dp_tiles, gp.sk_tiles);
+        if (gp.sk_tiles != 0) {
+            const uint64_t part = streamk_partial_bytes(clusters, cta, p.n1);
+            gp.sk_partials = static_cast<float*>(workspace);
+            gp.sk_sems = reinterpret_cast<int32_t*>(static_cast<char*>(workspace) + part);
+            // The counters are left at zero by the kernel (the last slice of a tile resets its counter), so they
+            // only need clearing the first time a workspace region is used for them.
+            static std::mutex mu;
+            static const void* cleared_ptr = nullptr;
+            static uint64_t cleared_bytes = 0;
+            const uint64_t sem_bytes = uint64_t(gp.sk_tiles) * cta * 4;
+            std::lock_guard<std::mutex> lock(mu);
+            if (cleared_ptr != gp.sk_sems || cleared_bytes < sem_bytes) {
+                DGA_CUDA(cudaMemsetAsync(gp.sk_sems, 0, sem_bytes, stream));
+                cleared_ptr = gp.sk_sems;
+                cleared_bytes = sem_bytes;
+            }
+        }
+    }
     static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
     gp.debug = dbg;
     if (cta == 2)
@@ -244,10 +267,16 @@ static int launch_splitk(DenseLaunch& L, cudaStream_t stream) {
     return ACLNN_ERR_PARAM_INVALID;
 }
 
-static int launch_dense(DenseLaunch& L, cudaStream_t stream) {
+static int launch_dense(DenseLaunch& L, cudaStream_t stream, void* workspace = nullptr) {
     switch (L.plan.kernelSerial) {
         case DGA_KERNEL_COMMON:
-        case DGA_KERNEL_SMALL: return launch_common(L, stream);
+        case DGA_KERNEL_SMALL: return launch_common(L, stream, nullptr);
+        case DGA_KERNEL_STREAMK:
+            if (workspace == nullptr) {
+                set_error("the stream-K variant needs its workspace");
+                return ACLNN_ERR_PARAM_INVALID;
+            }
+            return launch_common(L, stream, workspace);
         case DGA_KERNEL_SPLITK: return launch_splitk(L, stream);
     }
     set_error("kernel variant " + std::to_string(int(L.plan.kernelSerial)) + " is not built");
@@ -646,7 +675,7 @@ aclnnStatus aclnnCatlassDynamicMatmul(void* workspace, uint64_t workspaceSize, a
         set_error("workspace too small");
         rc = ACLNN_ERR_PARAM_INVALID;
     } else {
-        rc = launch_dense(executor->dense, static_cast<cudaStream_t>(stream));
+        rc = launch_dense(executor->dense, static_cast<cudaStream_t>(stream), workspace);
     }
     if (!executor->repeatable) delete executor;
     return rc;
@@ -663,7 +692,7 @@ aclnnStatus dgaDestroyExecutor(aclOpExecutor* executor) {
 }
 
 aclnnStatus dgaMatmulWithPlan(const aclTensor* self, const aclTensor* mat2, const aclTensor* out,
-                              const DgaTilingPlan* plan, void*, uint64_t, aclrtStream stream) {
+                              const DgaTilingPlan* plan, void* workspace, uint64_t workspaceSize, aclrtStream stream) {
     if (plan == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
     DenseLaunch L;
     aclnnStatus rc = validate_dense(self, mat2, out, L);
@@ -677,7 +706,11 @@ aclnnStatus dgaMatmulWithPlan(const aclTensor* self, const aclTensor* mat2, cons
     L.plan = p;
     rc = check_strides(L);
     if (rc != ACLNN_SUCCESS) return rc;
-    return launch_dense(L, static_cast<cudaStream_t>(stream));
+    if (workspaceSize < p.workspaceBytes) {
+        set_error("workspace too small: the plan needs " + std::to_string(p.workspaceBytes) + " bytes");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    return launch_dense(L, static_cast<cudaStream_t>(stream), workspace);
 }
 
 // ---- fp8 block-scaled ------------------------------------------------------------------------------------

@@ -51,6 +51,44 @@ struct GemmParams {
     uint32_t sf_m_chunks;    // ceil(m / 128)
     const int32_t* gate;     // device flag; the kernel runs only when *gate == gate_expect (nullptr: always)
     int32_t gate_expect;
+    // stream-K (role of PaddingStreamkMatmulKernel): the first dp_tiles tiles are walked whole, one per cluster
+    // and wave; the K blocks of the remaining sk_tiles tiles are dealt out evenly to all clusters.
+    uint32_t dp_tiles, sk_tiles;
+    float* sk_partials;      // [cluster][head/tail][cta rank][128][block_n] fp32
+    int32_t* sk_sems;        // [sk tile][cta rank] arrival counters, zero on entry and on exit
+};
+
+// One unit of work of a cluster: K blocks [kb0, kb1) of `tile`.  Every warp role walks the same sequence.
+struct WorkItem {
+    uint32_t tile, kb0, kb1;
+};
+struct WorkIter {
+    uint32_t clusters, cid, dp_tiles, kb_total;
+    uint32_t next_dp;
+    uint64_t u, u_end;       // stream-K units (tile-local index * kb_total + kb) still to do
+    __device__ __forceinline__ WorkIter(const GemmParams& p, uint32_t cluster_id, uint32_t num_clusters)
+        : clusters(num_clusters), cid(cluster_id), dp_tiles(p.dp_tiles), kb_total(p.k_blocks), next_dp(cluster_id) {
+        const uint64_t total = static_cast<uint64_t>(p.sk_tiles) * p.k_blocks;
+        u = begin_of(total, cluster_id, num_clusters);
+        u_end = begin_of(total, cluster_id + 1, num_clusters);
+    }
+    static __device__ __forceinline__ uint64_t begin_of(uint64_t total, uint32_t c, uint32_t clusters) {
+        return total * c / clusters;
+    }
+    __device__ __forceinline__ bool next(WorkItem& w) {
+        if (next_dp < dp_tiles) {
+            w.tile = next_dp; w.kb0 = 0; w.kb1 = kb_total;
+            next_dp += clusters;
+            return true;
+        }
+        if (u >= u_end) return false;
+        const uint32_t local = static_cast<uint32_t>(u / kb_total);
+        w.tile = dp_tiles + local;
+        w.kb0 = static_cast<uint32_t>(u - static_cast<uint64_t>(local) * kb_total);
+        w.kb1 = static_cast<uint32_t>(min(static_cast<uint64_t>(kb_total), w.kb0 + (u_end - u)));
+        u += w.kb1 - w.kb0;
+        return true;
+    }
 };
 
 // --- descriptors -----------------------------------------------------------
@@ -179,7 +217,6 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     const bool is_leader = cta_rank == 0;
     const uint32_t num_clusters = gridDim.x / kCta;
     const uint32_t cluster_id = blockIdx.x / kCta;
-    const uint32_t num_tiles = p.num_m_blocks * p.num_n_blocks;
     const uint32_t stages = p.num_stages;
 
     const uint32_t sf_stage_bytes = kMx ? 512u * (1u + p.sf_n_chunks) : 0u;
@@ -225,12 +262,14 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         // The whole warp walks the loop converged (uniform registers hold the addresses); one elected
         // lane issues.  A divergent `lane == 0` loop costs an ELECT/R2UR shuffle per operand.
         uint32_t stage = 0, phase = 0;
-        for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters) {
+        WorkIter it(p, cluster_id, num_clusters);
+        WorkItem w;
+        while (it.next(w)) {
             uint32_t mb, nb;
-            tile_coords(p, t, mb, nb);
+            tile_coords(p, w.tile, mb, nb);
             const int32_t m_idx = static_cast<int32_t>(mb * (kBlockM * kCta) + cta_rank * kBlockM);
             const int32_t n_idx = static_cast<int32_t>(nb * p.block_n + cta_rank * load_n);
-            for (uint32_t kb = 0; kb < p.k_blocks; ++kb) {
+            for (uint32_t kb = w.kb0; kb < w.kb1; ++kb) {
                 ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                 if (p.debug & 1) {
                     if (ptx::elect_one()) {
@@ -300,16 +339,18 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
             const uint32_t a_step = L.a_stage_bytes >> 4, b_step = L.b_stage_bytes >> 4;
             constexpr uint32_t kBStepLo = kBMn ? (16 * 128) >> 4 : 32 >> 4;  // one UMMA_K (16 elements) along K
             const uint32_t idesc = p.idesc;
-            const uint32_t k_blocks = p.k_blocks;
             const uint32_t tmem_sfa = tmem_base + 2 * p.block_n;   // 4 columns; B scales follow
             const uint32_t tmem_sfb = tmem_sfa + 4;
             uint32_t stage = 0, phase = 0, iter = 0;
-            for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters, ++iter) {
+            WorkIter it(p, cluster_id, num_clusters);
+            WorkItem w;
+            for (; it.next(w); ++iter) {
                 const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
                 ptx::mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
                 ptx::tc_fence_after();
                 const uint32_t tmem_d = tmem_base + as * p.block_n;
-                for (uint32_t kb = 0; kb < k_blocks; ++kb) {
+                const uint32_t kb0 = w.kb0, k_blocks = w.kb1;
+                for (uint32_t kb = kb0; kb < k_blocks; ++kb) {
                     ptx::mbar_wait(&full_bar[stage], phase);
                     ptx::tc_fence_after();
                     if (ptx::elect_one()) {
@@ -333,9 +374,9 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                             const uint64_t a_desc = (static_cast<uint64_t>(a_hi) << 32) | (a_lo + k * 2);
                             const uint64_t b_desc = (static_cast<uint64_t>(b_hi) << 32) | (b_lo + k * kBStepLo);
                             if constexpr (kMx)
-                                ptx::mma_mxf8<kCta>(tmem_d, a_desc, b_desc, idesc_k, tmem_sfa, tmem_sfb, (kb | k) != 0);
+                                ptx::mma_mxf8<kCta>(tmem_d, a_desc, b_desc, idesc_k, tmem_sfa, tmem_sfb, ((kb - kb0) | k) != 0);
                             else if (!(p.debug & 2))
-                                ptx::mma_f16<kCta>(tmem_d, a_desc, b_desc, idesc_k, (kb | k) != 0);
+                                ptx::mma_f16<kCta>(tmem_d, a_desc, b_desc, idesc_k, ((kb - kb0) | k) != 0);
                         }
                         ptx::mma_commit<kCta>(&empty_bar[stage]);
                         if (kb + 1 == k_blocks) ptx::mma_commit<kCta>(&tmem_full_bar[as]);
@@ -350,9 +391,29 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         const uint32_t epi_tid = threadIdx.x - 128;          // 0..127 == accumulator row == TMEM lane
         const uint32_t lane_base = (warp & 3) * 32;          // tcgen05.ld lane window of this warp
         uint32_t iter = 0, buf = 0;
-        for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters, ++iter) {
+        volatile uint32_t* sk_bcast = tmem_ptr_smem + 1;       // arrival count broadcast inside the epilogue warps
+        // one 32-column chunk of this CTA's rows: registers -> staging smem -> TMA store
+        auto store_chunk = [&](const uint32_t (&v)[32], uint32_t m0, uint32_t col) {
+            // staging buffer `buf` was last read by the store issued two chunks ago
+            if (epi_tid == 0) ptx::tma_store_wait_read<1>();
+            ptx::named_bar_sync(1, 128);
+            const uint32_t sbase = smem_base + L.off_d + buf * L.d_stage_bytes;
+            stage_row<OutT>(sbase, epi_tid, v);
+            ptx::fence_async_smem();
+            ptx::named_bar_sync(1, 128);
+            if (epi_tid == 0) {
+                if (m0 < p.m && !(p.debug & 4))
+                    ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes,
+                                      static_cast<int32_t>(col), static_cast<int32_t>(m0));
+                ptx::tma_store_commit();
+            }
+            buf ^= 1;
+        };
+        WorkIter it(p, cluster_id, num_clusters);
+        WorkItem w;
+        for (; it.next(w); ++iter) {
             uint32_t mb, nb;
-            tile_coords(p, t, mb, nb);
+            tile_coords(p, w.tile, mb, nb);
             const uint32_t m0 = mb * (kBlockM * kCta) + cta_rank * kBlockM;
             const uint32_t n0 = nb * p.block_n;
             const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
@@ -362,30 +423,90 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
             ptx::mbar_wait(&tmem_full_bar[as], aphase);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + (lane_base << 16) + as * p.block_n;
-            for (uint32_t c = 0; c < chunks; ++c) {
-                uint32_t v[32];
-                ptx::tmem_ld_32x32(taddr + c * kEpiCols, v);
-                ptx::tmem_ld_wait();
-                if (c + 1 == chunks) {
-                    // accumulator fully read: hand the TMEM stage back to the issuer
-                    ptx::tc_fence_before();
-                    if constexpr (kCta == 2) ptx::mbar_arrive_remote(&tmem_empty_bar[as], 0);
-                    else ptx::mbar_arrive(&tmem_empty_bar[as]);
+            auto release_tmem = [&]() {
+                // accumulator fully read: hand the TMEM stage back to the issuer
+                ptx::tc_fence_before();
+                if constexpr (kCta == 2) ptx::mbar_arrive_remote(&tmem_empty_bar[as], 0);
+                else ptx::mbar_arrive(&tmem_empty_bar[as]);
+            };
+            if (w.kb1 - w.kb0 == p.k_blocks) {
+                for (uint32_t c = 0; c < chunks; ++c) {
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32(taddr + c * kEpiCols, v);
+                    ptx::tmem_ld_wait();
+                    if (c + 1 == chunks) release_tmem();
+                    store_chunk(v, m0, n0 + c * kEpiCols);
                 }
-                // staging buffer `buf` was last read by the store issued two chunks ago
-                if (epi_tid == 0) ptx::tma_store_wait_read<1>();
-                ptx::named_bar_sync(1, 128);
-                const uint32_t sbase = smem_base + L.off_d + buf * L.d_stage_bytes;
-                stage_row<OutT>(sbase, epi_tid, v);
-                ptx::fence_async_smem();
-                ptx::named_bar_sync(1, 128);
-                if (epi_tid == 0) {
-                    if (m0 < p.m && !(p.debug & 4))
-                        ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes,
-                                          static_cast<int32_t>(n0 + c * kEpiCols), static_cast<int32_t>(m0));
-                    ptx::tma_store_commit();
+            } else {
+                // ---- stream-K slice: fp32 partial -> workspace; the last slice of the tile to arrive adds them up
+                // in a fixed order (deterministic) and stores the tile.
+                const uint64_t total = static_cast<uint64_t>(p.sk_tiles) * p.k_blocks;
+                const uint64_t u_tile = static_cast<uint64_t>(w.tile - p.dp_tiles) * p.k_blocks;
+                const uint64_t slot_floats = static_cast<uint64_t>(kBlockM) * p.block_n;
+                auto slot_of = [&](uint32_t cluster) {
+                    // a cluster's slice of this tile is its head (it starts where the cluster's range starts) or its tail
+                    const uint32_t which = WorkIter::begin_of(total, cluster, num_clusters) >= u_tile ? 0u : 1u;
+                    return p.sk_partials + ((static_cast<uint64_t>(cluster) * 2 + which) * kCta + cta_rank) * slot_floats;
+                };
+                // slot layout [chunk][4-column group][row] of 16-byte words: a warp's 32 rows are contiguous
+                uint4* mine = reinterpret_cast<uint4*>(slot_of(cluster_id)) + epi_tid;
+                for (uint32_t c = 0; c < chunks; ++c) {
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32(taddr + c * kEpiCols, v);
+                    ptx::tmem_ld_wait();
+                    if (c + 1 == chunks) release_tmem();
+#pragma unroll
+                    for (uint32_t j = 0; j < 8; ++j)
+                        __stcg(mine + (c * 8 + j) * kBlockM, make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
                 }
-                buf ^= 1;
+                __threadfence();
+                ptx::named_bar_sync(1, 128);
+                int32_t* sem = p.sk_sems + (w.tile - p.dp_tiles) * kCta + cta_rank;
+                if (epi_tid == 0) *sk_bcast = static_cast<uint32_t>(atomicAdd(sem, 1));
+                ptx::named_bar_sync(1, 128);
+                const uint32_t arrived = *sk_bcast;
+                // clusters whose ranges touch this tile: owner(u) = ceil((u + 1) * clusters / total) - 1
+                const uint32_t first = static_cast<uint32_t>(((u_tile + 1) * num_clusters + total - 1) / total) - 1;
+                const uint32_t last = static_cast<uint32_t>(((u_tile + p.k_blocks) * num_clusters + total - 1) / total) - 1;
+                if (arrived == last - first && (p.debug & 8)) {
+                    if (epi_tid == 0) *sem = 0;   // isolation: skip the reduction
+                } else if (arrived == last - first) {
+                    __threadfence();
+                    for (uint32_t c = 0; c < chunks; ++c) {
+                        float acc[32];
+#pragma unroll
+                        for (uint32_t j = 0; j < 32; ++j) acc[j] = 0.f;
+                        // three slices at a time: 24 independent 16-byte loads in flight per thread hide the L2 latency
+                        for (uint32_t q = first; q <= last; q += 3) {
+                            uint4 t4[3][8];
+#pragma unroll
+                            for (uint32_t i = 0; i < 3; ++i) {
+                                if (q + i <= last) {
+                                    const uint4* src = reinterpret_cast<const uint4*>(slot_of(q + i)) + epi_tid + c * 8 * kBlockM;
+#pragma unroll
+                                    for (uint32_t j = 0; j < 8; ++j) t4[i][j] = __ldcg(src + j * kBlockM);
+                                }
+                            }
+#pragma unroll
+                            for (uint32_t i = 0; i < 3; ++i) {
+                                if (q + i <= last) {
+#pragma unroll
+                                    for (uint32_t j = 0; j < 8; ++j) {
+                                        acc[4 * j + 0] += __uint_as_float(t4[i][j].x);
+                                        acc[4 * j + 1] += __uint_as_float(t4[i][j].y);
+                                        acc[4 * j + 2] += __uint_as_float(t4[i][j].z);
+                                        acc[4 * j + 3] += __uint_as_float(t4[i][j].w);
+                                    }
+                                }
+                            }
+                        }
+                        uint32_t v[32];
+#pragma unroll
+                        for (uint32_t j = 0; j < 32; ++j) v[j] = __float_as_uint(acc[j]);
+                        store_chunk(v, m0, n0 + c * kEpiCols);
+                    }
+                    if (epi_tid == 0) *sem = 0;   // ready for the next launch
+                }
             }
         }
         if (epi_tid == 0) ptx::tma_store_wait_all<0>();

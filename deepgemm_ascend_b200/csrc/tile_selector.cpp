@@ -142,6 +142,22 @@ bool aligned16(uint64_t elems, uint32_t bytes) { return (elems * bytes) % 16 == 
 
 }  // namespace
 
+void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t& dp, uint32_t& sk) {
+    const uint32_t full = tiles / clusters, rem = tiles % clusters;
+    dp = tiles;
+    sk = 0;
+    if (rem == 0) return;
+    // hand the ragged last wave plus (when there is one) a whole wave to stream-K, so that no slice is thin
+    const uint32_t sk_try = full >= 1 ? clusters + rem : tiles;
+    if (uint64_t(sk_try) * kb < 2ull * clusters) return;
+    sk = sk_try;
+    dp = tiles - sk;
+}
+
+uint64_t streamk_partial_bytes(uint32_t clusters, uint32_t cta_group, uint32_t block_n) {
+    return uint64_t(clusters) * 2 * cta_group * 128 * block_n * 4;
+}
+
 int finalize_plan(DgaTilingPlan& p) {
     const PlatformInfo& hw = platform();
     const uint32_t in_b = elem_bytes(p.dtype), out_b = elem_bytes(p.outDtype);
@@ -180,6 +196,22 @@ int finalize_plan(DgaTilingPlan& p) {
         p.blockDim = std::min(tiles, hw.smCount / cta) * cta;
         p.smemBytes = common_smem_bytes(p.n1, cta, p.stages, out_b, in_b);
         p.workspaceBytes = 0;
+        if (p.kernelSerial == DGA_KERNEL_STREAMK) {
+            const uint32_t clusters = hw.smCount / cta;
+            uint32_t dp, sk;
+            streamk_split(tiles, clusters, ceil_div(p.k, 128 / in_b), dp, sk);
+            if (sk == 0) {
+                p.kernelSerial = tiles <= clusters ? DGA_KERNEL_SMALL : DGA_KERNEL_COMMON;
+            } else {
+                p.blockDim = clusters * cta;
+                p.workspaceBytes = streamk_partial_bytes(clusters, cta, p.n1) + ((uint64_t(sk) * cta * 4 + 255) & ~255ull);
+            }
+        } else if (p.kernelSerial != DGA_KERNEL_SMALL && p.kernelSerial != DGA_KERNEL_COMMON) {
+            set_error("kernel variant " + std::to_string(int(p.kernelSerial)) + " is not built");
+            return ACLNN_ERR_INNER_TILING_ERROR;
+        } else {
+            p.kernelSerial = tiles <= hw.smCount / cta ? DGA_KERNEL_SMALL : DGA_KERNEL_COMMON;
+        }
         if (p.splitkFactor == 0) p.splitkFactor = 1;
     }
     if (p.swizzleOffset == 0) p.swizzleOffset = 8;
@@ -233,7 +265,9 @@ int select_kernel(DgaTilingPlan& p) {
     }
     // M <= 64 is HBM-bound by the weight: a 256-row pair tile would waste >= 3/4 of the tensor work and, worse,
     // most of the SMs' load slots, so the streaming kernel always wins there; above that the estimates decide.
-    if (sbest.split != 0 && (sbest.us < best.us || p.m <= 64)) {
+    // measured on B200 (N=4096, K=7168): the swap-AB kernel also wins at M = 128 (20.6 vs 28.9 us) and M = 256
+    // (24.7 vs 29.0 us); the estimates are too coarse there, so the rule is explicit.
+    if (sbest.split != 0 && (sbest.us < best.us || p.m <= 256)) {
         p.kernelSerial = DGA_KERNEL_SPLITK;
         p.splitkFactor = static_cast<uint16_t>(sbest.split);
         p.stages = static_cast<uint8_t>(sbest.stages);

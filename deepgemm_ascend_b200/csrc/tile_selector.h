@@ -42,6 +42,13 @@ int select_kernel(DgaTilingPlan& plan);
 int finalize_plan(DgaTilingPlan& plan);
 int select_kernel_with_cache(DgaTilingPlan& plan);
 
+// Stream-K decomposition of `tiles` output tiles of `kb` K blocks over `clusters` clusters: the first `dp` tiles are
+// walked whole (one per cluster and wave), the K blocks of the last `sk` tiles are dealt out evenly.  sk == 0 when
+// the tiles already fill whole waves or the slices would be too thin.
+void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t& dp, uint32_t& sk);
+// Workspace layout of the stream-K variant: fp32 partial slots, then the per-tile arrival counters.
+uint64_t streamk_partial_bytes(uint32_t clusters, uint32_t cta_group, uint32_t block_n);
+
 // plan_cache.cpp
 int cache_get(DgaTilingPlan& plan);  // keyed by (m, n, k, dtype, outDtype, layoutTagB) already set in `plan`
 int cache_set(const DgaTilingPlan& plan);

@@ -78,6 +78,13 @@ ACLNN_CASES = [
     (16, 584, 2016, torch.float16, 1, {}),                   # custom_catlass demo shape 16x578x2014, 16 B-aligned
     (512, 4096, 7168, torch.bfloat16, 1, {}),
     (2048, 4096, 2048, torch.bfloat16, 1, {}),
+    # stream-K variant (role of PaddingStreamkMatmulKernel): K blocks of the ragged wave dealt out to every cluster
+    (512, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 256}),
+    (128, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 1, "n1": 128}),
+    (1000, 1000, 1000, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 128}),
+    (300, 520, 1992, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 1, "n1": 64}),
+    (2048, 4096, 2048, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 256}),
+    (640, 1024, 1024, torch.float16, 0, {"kernelSerial": 4, "ctaGroup": 2, "n1": 128}),
 ]
 
 
