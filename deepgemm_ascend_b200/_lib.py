@@ -76,6 +76,9 @@ SIGNATURES = {
     "dgaRunMmadBench": (_i32, [_vp, _vp, _vp, _u32, _u32, _u32, _P(_i32), _vp]),
     "dgaGetBenchConfig": (_i32, [_u32, _u32, _u32, _P(_i32)]),
     "dgaNShardRange": (_i32, [_u32, _u32, _u32, _P(_u32), _P(_u32)]),
+    "dgaNShardMatmulGetWorkspaceSize": (_i32, [_P(AclTensor), _P(AclTensor), _P(_vp), _u32, _u32, ctypes.c_int64,
+                                            ctypes.c_int64, _P(_u64), _P(_vp)]),
+    "dgaNShardMatmul": (_i32, [_vp, _u64, _vp, _vp]),
     "dgaGetLastError": (ctypes.c_char_p, []),
     "dgaKernelLaunchCount": (_u64, []),
     "dgaVersion": (ctypes.c_char_p, []),

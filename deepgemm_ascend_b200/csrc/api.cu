@@ -94,6 +94,10 @@ struct DenseLaunch {
     uint64_t lda, ldb, ldd;  // elements
     CUtensorMap tm_a, tm_b, tm_d;
     bool encoded = false;
+    // N-sharded execution: the column slice of every peer's C (device pointers mapped into this process)
+    uint32_t num_peers = 0;
+    void* peer_d[kMaxPeers] = {};
+    PeerMaps peers{};
 };
 
 // cudaFuncSetAttribute costs microseconds of host time; remember the largest opt-in per kernel instance.
@@ -126,7 +130,7 @@ static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaSt
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, L.tm_a, L.tm_b, gp));  // no scale maps here
+    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, L.tm_a, L.tm_b, L.peers, gp));  // no scale maps here
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
 }
@@ -153,8 +157,12 @@ static int encode_common(DenseLaunch& L) {
         rc = make_tmap_2d(&L.tm_b, L.b, p.dtype, p.n, p.k, L.ldb, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != ACLNN_SUCCESS) return rc;
     const bool wide = elem_bytes(p.outDtype) == 4;
-    return make_tmap_2d(&L.tm_d, L.d, p.outDtype, p.n, p.m, L.ldd, 32, 128,
-                        wide ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B);
+    const CUtensorMapSwizzle d_swz = wide ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    for (uint32_t i = 0; i < L.num_peers; ++i) {
+        rc = make_tmap_2d(&L.peers.m[i], L.peer_d[i], p.outDtype, p.n, p.m, L.ldd, 32, 128, d_swz);
+        if (rc != ACLNN_SUCCESS) return rc;
+    }
+    return make_tmap_2d(&L.tm_d, L.d, p.outDtype, p.n, p.m, L.ldd, 32, 128, d_swz);
 }
 
 static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
@@ -177,6 +185,7 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     gp.idesc = make_idesc(128 * cta, p.n1, p.dtype == ACL_BF16 ? 1u : 0u, 0, p.layoutTagB == 1 ? 0u : 1u);
     gp.b_stage_bytes = (p.n1 / cta) * 128;
     gp.k_block_elems = 64;
+    gp.num_peers = L.num_peers;
     gp.dp_tiles = gp.num_m_blocks * gp.num_n_blocks;
     gp.sk_tiles = 0;
     if (p.kernelSerial == DGA_KERNEL_STREAMK) {
@@ -439,7 +448,8 @@ static int launch_mx_inst(const Fp8Launch& L, const GemmParams& gp, cudaStream_t
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b_mx, L.tm_d, L.tm_sfa, L.tm_sfb, gp));
+    static const PeerMaps no_peers{};
+    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b_mx, L.tm_d, L.tm_sfa, L.tm_sfb, no_peers, gp));
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
 }
@@ -711,6 +721,70 @@ aclnnStatus dgaMatmulWithPlan(const aclTensor* self, const aclTensor* mat2, cons
         return ACLNN_ERR_PARAM_INVALID;
     }
     return launch_dense(L, static_cast<cudaStream_t>(stream), workspace);
+}
+
+// ---- N-sharded matmul with the gather of C fused into the epilogue ----------------------------------------------
+aclnnStatus dgaNShardMatmulGetWorkspaceSize(const aclTensor* self, const aclTensor* mat2Shard, void* const* outPeers,
+                                            uint32_t worldSize, uint32_t rank, int64_t nTotal, int64_t ldOut,
+                                            uint64_t* workspaceSize, aclOpExecutor** executor) {
+    if (outPeers == nullptr || workspaceSize == nullptr || executor == nullptr || self == nullptr || mat2Shard == nullptr) {
+        set_error("null argument");
+        return ACLNN_ERR_PARAM_NULLPTR;
+    }
+    if (worldSize == 0 || worldSize > kMaxPeers + 1 || rank >= worldSize) {
+        set_error("N-sharded matmul supports 1.." + std::to_string(kMaxPeers + 1) + " ranks");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (mat2Shard->ndim != 2 || nTotal <= 0 || nTotal > UINT32_MAX || ldOut < nTotal) {
+        set_error("bad N-shard geometry");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    uint32_t n_begin = 0, n_count = 0;
+    aclnnStatus rc = dgaNShardRange(uint32_t(nTotal), worldSize, rank, &n_begin, &n_count);
+    if (rc != ACLNN_SUCCESS) return rc;
+    if (mat2Shard->shape[1] != int64_t(n_count)) {
+        set_error("mat2 shard must hold columns [" + std::to_string(n_begin) + ", " + std::to_string(n_begin + n_count) +
+                  ") of the weight");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    // out = this rank's column slice of its own full C; peers get the same slice of theirs
+    const uint32_t eb = elem_bytes(self->dtype);
+    aclTensor out{};
+    out.dtype = self->dtype;
+    out.ndim = 2;
+    out.shape[0] = self->shape[0]; out.shape[1] = n_count;
+    out.stride[0] = ldOut; out.stride[1] = 1;
+    out.data = static_cast<char*>(outPeers[rank]) + uint64_t(n_begin) * eb;
+    aclOpExecutor* ex = new aclOpExecutor{};
+    rc = validate_dense(self, mat2Shard, &out, ex->dense);
+    if (rc == ACLNN_SUCCESS) {
+        // the persistent kernel carries the peer stores; small-M and stream-K variants are not used here
+        DgaTilingPlan& p = ex->dense.plan;
+        rc = select_kernel_with_cache(p);
+        if (rc == ACLNN_SUCCESS && p.kernelSerial != DGA_KERNEL_COMMON && p.kernelSerial != DGA_KERNEL_SMALL) {
+            DgaTilingPlan q{};
+            q.m = p.m; q.n = p.n; q.k = p.k; q.dtype = p.dtype; q.outDtype = p.outDtype; q.layoutTagB = p.layoutTagB;
+            q.kernelSerial = DGA_KERNEL_COMMON; q.ctaGroup = 2; q.n1 = p.layoutTagB ? 128 : 128;
+            rc = finalize_plan(q);
+            if (rc == ACLNN_SUCCESS) { q.strideA = p.strideA; q.strideB = p.strideB; q.strideC = p.strideC; p = q; }
+        }
+    }
+    if (rc == ACLNN_SUCCESS) rc = check_strides(ex->dense);
+    if (rc != ACLNN_SUCCESS) {
+        delete ex;
+        return rc;
+    }
+    for (uint32_t r = 0, i = 0; r < worldSize; ++r) {
+        if (r == rank) continue;
+        ex->dense.peer_d[i++] = static_cast<char*>(outPeers[r]) + uint64_t(n_begin) * eb;
+    }
+    ex->dense.num_peers = worldSize - 1;
+    *workspaceSize = ex->dense.plan.workspaceBytes;
+    *executor = ex;
+    return ACLNN_SUCCESS;
+}
+aclnnStatus dgaNShardMatmul(void* workspace, uint64_t workspaceSize, aclOpExecutor* executor, aclrtStream stream) {
+    return aclnnCatlassDynamicMatmul(workspace, workspaceSize, executor, stream);
 }
 
 // ---- fp8 block-scaled ------------------------------------------------------------------------------------

@@ -54,8 +54,17 @@ struct GemmParams {
     // stream-K (role of PaddingStreamkMatmulKernel): the first dp_tiles tiles are walked whole, one per cluster
     // and wave; the K blocks of the remaining sk_tiles tiles are dealt out evenly to all clusters.
     uint32_t dp_tiles, sk_tiles;
+    uint32_t num_peers;      // extra destinations of every output chunk (PeerMaps)
     float* sk_partials;      // [cluster][head/tail][cta rank][128][block_n] fp32
     int32_t* sk_sems;        // [sk tile][cta rank] arrival counters, zero on entry and on exit
+};
+
+// N-sharded execution (BASELINE config 5): besides its own C, a rank's epilogue stores every finished chunk
+// straight into the same column slice of each peer's C over NVLink (TMA stores on peer-mapped addresses), so
+// the all-gather of C rides on the GEMM tile by tile instead of following it.
+constexpr uint32_t kMaxPeers = 7;
+struct PeerMaps {
+    CUtensorMap m[kMaxPeers];
 };
 
 // One unit of work of a cluster: K blocks [kb0, kb1) of `tile`.  Every warp role walks the same sequence.
@@ -204,7 +213,8 @@ template <int kCta, typename OutT, bool kBMn, bool kMx = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                   const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_sfa,
-                  const __grid_constant__ CUtensorMap tm_sfb, const GemmParams p) {
+                  const __grid_constant__ CUtensorMap tm_sfb, const __grid_constant__ PeerMaps peers,
+                  const GemmParams p) {
     static_assert(!(kMx && kBMn), "block-scaled fp8 wants K-major operands");
     if (p.gate != nullptr && *p.gate != p.gate_expect) return;   // grid-uniform
     extern __shared__ uint8_t smem_raw[];
@@ -402,9 +412,13 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
             ptx::fence_async_smem();
             ptx::named_bar_sync(1, 128);
             if (epi_tid == 0) {
-                if (m0 < p.m && !(p.debug & 4))
+                if (m0 < p.m && !(p.debug & 4)) {
                     ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes,
                                       static_cast<int32_t>(col), static_cast<int32_t>(m0));
+                    for (uint32_t i = 0; i < p.num_peers; ++i)   // same chunk into every peer's C (NVLink)
+                        ptx::tma_store_2d(&peers.m[i], smem + L.off_d + buf * L.d_stage_bytes,
+                                          static_cast<int32_t>(col), static_cast<int32_t>(m0));
+                }
                 ptx::tma_store_commit();
             }
             buf ^= 1;
