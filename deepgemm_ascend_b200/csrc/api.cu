@@ -156,13 +156,14 @@ static int encode_common(DenseLaunch& L) {
     else  // row-major [K, N]: boxes of 64 columns x 64 k-rows
         rc = make_tmap_2d(&L.tm_b, L.b, p.dtype, p.n, p.k, L.ldb, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != ACLNN_SUCCESS) return rc;
-    const bool wide = elem_bytes(p.outDtype) == 4;
+    const uint32_t epi = epi_cols_for(p.n1, elem_bytes(p.outDtype));
+    const bool wide = epi * elem_bytes(p.outDtype) == 128;
     const CUtensorMapSwizzle d_swz = wide ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
     for (uint32_t i = 0; i < L.num_peers; ++i) {
-        rc = make_tmap_2d(&L.peers.m[i], L.peer_d[i], p.outDtype, p.n, p.m, L.ldd, 32, 128, d_swz);
+        rc = make_tmap_2d(&L.peers.m[i], L.peer_d[i], p.outDtype, p.n, p.m, L.ldd, epi, 128, d_swz);
         if (rc != ACLNN_SUCCESS) return rc;
     }
-    return make_tmap_2d(&L.tm_d, L.d, p.outDtype, p.n, p.m, L.ldd, 32, 128, d_swz);
+    return make_tmap_2d(&L.tm_d, L.d, p.outDtype, p.n, p.m, L.ldd, epi, 128, d_swz);
 }
 
 static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
@@ -186,6 +187,7 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     gp.b_stage_bytes = (p.n1 / cta) * 128;
     gp.k_block_elems = 64;
     gp.num_peers = L.num_peers;
+    gp.epi_cols = epi_cols_for(p.n1, elem_bytes(p.outDtype));
     gp.dp_tiles = gp.num_m_blocks * gp.num_n_blocks;
     gp.sk_tiles = 0;
     if (p.kernelSerial == DGA_KERNEL_STREAMK) {
@@ -303,7 +305,7 @@ struct Fp8Launch {
     // hardware block-scaled path (scales that are exact powers of two)
     uint32_t mx_cta = 2, mx_bn = 224, mx_stages = 0, mx_grid = 0, mx_smem = 0, mx_chunks = 2;
     uint64_t ws_sfa_off = 0, ws_sfb_off = 0, ws_flag_off = 0, ws_bytes = 0;
-    CUtensorMap tm_b_mx, tm_sfa, tm_sfb;
+    CUtensorMap tm_b_mx, tm_d_mx, tm_sfa, tm_sfb;
     const void* encoded_ws = nullptr;
 };
 
@@ -348,11 +350,12 @@ static void plan_fp8(Fp8Launch& L) {
     L.mx_chunks = ceil_div(L.mx_bn, 128);
     const uint32_t sf_stage = 512 * (1 + L.mx_chunks);
     const uint32_t mx_per_stage = 128 * 128 + (L.mx_bn / L.mx_cta) * 128 + sf_stage;
-    const uint32_t mx_fixed = 2 * 128 * 32 * 2 + 1024 + 256;
+    const uint32_t mx_d_stage = 128 * epi_cols_for(L.mx_bn, 2) * 2;
+    const uint32_t mx_fixed = 2 * mx_d_stage + 1024 + 256;
     L.mx_stages = std::min<uint32_t>(10, (hw.smemBytes - mx_fixed) / mx_per_stage);
     const uint32_t mx_tiles = ceil_div(L.m, 128 * L.mx_cta) * ceil_div(L.n, L.mx_bn);
     L.mx_grid = std::min(mx_tiles, hw.smCount / L.mx_cta) * L.mx_cta;
-    L.mx_smem = make_smem_layout(2, (L.mx_bn / L.mx_cta) * 128, L.mx_stages, sf_stage).total + 1024;
+    L.mx_smem = make_smem_layout(mx_d_stage, (L.mx_bn / L.mx_cta) * 128, L.mx_stages, sf_stage).total + 1024;
     // workspace: packed A scales [K/512][ceil(M/128)][128] words, packed B scales [K/512][n tiles][chunks][128], flag
     const uint64_t kg = ceil_div(L.k, 512);
     L.ws_sfa_off = 0;
@@ -449,7 +452,7 @@ static int launch_mx_inst(const Fp8Launch& L, const GemmParams& gp, cudaStream_t
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     static const PeerMaps no_peers{};
-    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b_mx, L.tm_d, L.tm_sfa, L.tm_sfb, no_peers, gp));
+    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b_mx, L.tm_d_mx, L.tm_sfa, L.tm_sfb, no_peers, gp));
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
 }
@@ -467,6 +470,10 @@ static int launch_fp8(Fp8Launch& L, void* workspace, cudaStream_t stream) {
                           CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc != ACLNN_SUCCESS) return rc;
         rc = make_tmap_2d(&L.tm_d, L.d, ACL_BF16, L.n, L.m, L.ldd, 32, 128, CU_TENSOR_MAP_SWIZZLE_64B);
+        if (rc != ACLNN_SUCCESS) return rc;
+        const uint32_t epi = epi_cols_for(L.mx_bn, 2);
+        rc = make_tmap_2d(&L.tm_d_mx, L.d, ACL_BF16, L.n, L.m, L.ldd, epi, 128,
+                          epi == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B);
         if (rc != ACLNN_SUCCESS) return rc;
         L.encoded = true;
     }
@@ -507,6 +514,9 @@ static int launch_fp8(Fp8Launch& L, void* workspace, cudaStream_t stream) {
         gp.b_stage_bytes = (L.mx_bn / L.mx_cta) * 128;
         gp.k_block_elems = 128;
         gp.sf_n_chunks = L.mx_chunks;
+        gp.epi_cols = epi_cols_for(L.mx_bn, 2);
+        gp.dp_tiles = gp.num_m_blocks * gp.num_n_blocks;   // whole tiles only: the scale words come in groups of 4 K blocks
+        gp.sk_tiles = 0;
         gp.sf_m_chunks = m_chunks;
         gp.gate = mode == 0 ? flag : nullptr;
         gp.gate_expect = 0;

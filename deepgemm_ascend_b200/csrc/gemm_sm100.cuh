@@ -55,6 +55,7 @@ struct GemmParams {
     // and wave; the K blocks of the remaining sk_tiles tiles are dealt out evenly to all clusters.
     uint32_t dp_tiles, sk_tiles;
     uint32_t num_peers;      // extra destinations of every output chunk (PeerMaps)
+    uint32_t epi_cols;       // columns per TMA store: 32, or 64 for 16-bit outputs when block_n % 64 == 0 (128-byte rows)
     float* sk_partials;      // [cluster][head/tail][cta rank][128][block_n] fp32
     int32_t* sk_sems;        // [sk tile][cta rank] arrival counters, zero on entry and on exit
 };
@@ -161,17 +162,21 @@ template <> struct OutPack<__half> {
 // tile, in the swizzle the TMA store descriptor expects (SWIZZLE_64B for
 // 2-byte outputs: 64 B rows; SWIZZLE_128B for fp32: 128 B rows).
 template <typename OutT>
-__device__ __forceinline__ void stage_row(uint32_t stage_base, uint32_t row, const uint32_t (&v)[32]) {
+__device__ __forceinline__ void stage_row(uint32_t stage_base, uint32_t row, const uint32_t (&v)[32], uint32_t half = 0,
+                                          bool wide = false) {
     if constexpr (sizeof(OutT) == 2) {
-        const uint32_t row_base = stage_base + row * 64;
-        const uint32_t x = (row >> 1) & 3;
+        // narrow: 64-byte rows, SWIZZLE_64B; wide: 128-byte rows (two 32-column halves), SWIZZLE_128B
+        const uint32_t row_base = stage_base + row * (wide ? 128 : 64);
+        const uint32_t x = wide ? (row & 7) : ((row >> 1) & 3);
+        const uint32_t j0 = half * 4;
 #pragma unroll
-        for (uint32_t j = 0; j < 4; ++j) {
+        for (uint32_t jj = 0; jj < 4; ++jj) {
+            const uint32_t j = jj;
             const uint32_t a = OutPack<OutT>::pack(__uint_as_float(v[8 * j + 0]), __uint_as_float(v[8 * j + 1]));
             const uint32_t b = OutPack<OutT>::pack(__uint_as_float(v[8 * j + 2]), __uint_as_float(v[8 * j + 3]));
             const uint32_t c = OutPack<OutT>::pack(__uint_as_float(v[8 * j + 4]), __uint_as_float(v[8 * j + 5]));
             const uint32_t d = OutPack<OutT>::pack(__uint_as_float(v[8 * j + 6]), __uint_as_float(v[8 * j + 7]));
-            ptx::st_shared_v4(row_base + ((j ^ x) << 4), a, b, c, d);
+            ptx::st_shared_v4(row_base + (((j0 + j) ^ x) << 4), a, b, c, d);
         }
     } else {
         const uint32_t row_base = stage_base + row * 128;
@@ -188,10 +193,14 @@ struct SmemLayout {
     uint32_t d_stage_bytes, a_stage_bytes, b_stage_bytes, sf_stage_bytes;
     uint32_t off_d, off_a, off_b, off_sf, off_bar, total;
 };
-__host__ __device__ inline SmemLayout make_smem_layout(uint32_t out_elem_bytes, uint32_t b_stage_bytes, uint32_t stages,
+// Columns per output store: 128-byte rows whenever the tile allows it (full NVLink / L2 write lines).
+__host__ __device__ inline uint32_t epi_cols_for(uint32_t block_n, uint32_t out_elem_bytes) {
+    return (out_elem_bytes == 2 && block_n % 64 == 0) ? 64u : 32u;
+}
+__host__ __device__ inline SmemLayout make_smem_layout(uint32_t d_stage_bytes, uint32_t b_stage_bytes, uint32_t stages,
                                                        uint32_t sf_stage_bytes = 0) {
     SmemLayout l;
-    l.d_stage_bytes = kBlockM * kEpiCols * out_elem_bytes;
+    l.d_stage_bytes = d_stage_bytes;
     l.a_stage_bytes = kBlockM * kBlockKBytes;
     l.b_stage_bytes = b_stage_bytes;
     l.off_d = 0;
@@ -230,7 +239,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     const uint32_t stages = p.num_stages;
 
     const uint32_t sf_stage_bytes = kMx ? 512u * (1u + p.sf_n_chunks) : 0u;
-    const SmemLayout L = make_smem_layout(sizeof(OutT), p.b_stage_bytes, stages, sf_stage_bytes);
+    const SmemLayout L = make_smem_layout(kBlockM * p.epi_cols * sizeof(OutT), p.b_stage_bytes, stages, sf_stage_bytes);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.off_bar);
     uint64_t* empty_bar = full_bar + stages;
     uint64_t* tmem_full_bar = empty_bar + stages;
@@ -403,21 +412,26 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         uint32_t iter = 0, buf = 0;
         volatile uint32_t* sk_bcast = tmem_ptr_smem + 1;       // arrival count broadcast inside the epilogue warps
         // one 32-column chunk of this CTA's rows: registers -> staging smem -> TMA store
-        auto store_chunk = [&](const uint32_t (&v)[32], uint32_t m0, uint32_t col) {
-            // staging buffer `buf` was last read by the store issued two chunks ago
-            if (epi_tid == 0) ptx::tma_store_wait_read<1>();
-            ptx::named_bar_sync(1, 128);
+        const bool wide = p.epi_cols == 64;
+        auto store_chunk = [&](const uint32_t (&v)[32], uint32_t m0, uint32_t col, uint32_t c, bool last) {
+            const uint32_t half = wide ? (c & 1u) : 0u;
+            if (half == 0) {
+                // staging buffer `buf` was last read by the store issued two stores ago
+                if (epi_tid == 0) ptx::tma_store_wait_read<1>();
+                ptx::named_bar_sync(1, 128);
+            }
             const uint32_t sbase = smem_base + L.off_d + buf * L.d_stage_bytes;
-            stage_row<OutT>(sbase, epi_tid, v);
+            stage_row<OutT>(sbase, epi_tid, v, half, wide);
+            if (wide && half == 0 && !last) return;   // the second half of the 128-byte rows follows
             ptx::fence_async_smem();
             ptx::named_bar_sync(1, 128);
             if (epi_tid == 0) {
+                const int32_t c0 = static_cast<int32_t>(col - half * kEpiCols);
                 if (m0 < p.m && !(p.debug & 4)) {
-                    ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes,
-                                      static_cast<int32_t>(col), static_cast<int32_t>(m0));
+                    ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes, c0, static_cast<int32_t>(m0));
                     for (uint32_t i = 0; i < p.num_peers; ++i)   // same chunk into every peer's C (NVLink)
-                        ptx::tma_store_2d(&peers.m[i], smem + L.off_d + buf * L.d_stage_bytes,
-                                          static_cast<int32_t>(col), static_cast<int32_t>(m0));
+                        ptx::tma_store_2d(&peers.m[i], smem + L.off_d + buf * L.d_stage_bytes, c0,
+                                          static_cast<int32_t>(m0));
                 }
                 ptx::tma_store_commit();
             }
@@ -449,7 +463,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                     ptx::tmem_ld_32x32(taddr + c * kEpiCols, v);
                     ptx::tmem_ld_wait();
                     if (c + 1 == chunks) release_tmem();
-                    store_chunk(v, m0, n0 + c * kEpiCols);
+                    store_chunk(v, m0, n0 + c * kEpiCols, c, c + 1 == chunks);
                 }
             } else {
                 // ---- stream-K slice: fp32 partial -> workspace; the last slice of the tile to arrive adds them up
@@ -517,7 +531,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                         uint32_t v[32];
 #pragma unroll
                         for (uint32_t j = 0; j < 32; ++j) v[j] = __float_as_uint(acc[j]);
-                        store_chunk(v, m0, n0 + c * kEpiCols);
+                        store_chunk(v, m0, n0 + c * kEpiCols, c, c + 1 == chunks);
                     }
                     if (epi_tid == 0) *sem = 0;   // ready for the next launch
                 }

@@ -34,7 +34,7 @@ const char* last_error() { return g_last_error.c_str(); }
 uint32_t common_smem_bytes(uint32_t block_n, uint32_t cta_group, uint32_t stages, uint32_t out_bytes,
                            uint32_t in_bytes) {
     (void)in_bytes;  // a stage is always one 128-byte swizzle atom along K
-    const uint32_t d_stage = 128 * 32 * out_bytes;
+    const uint32_t d_stage = 128 * epi_cols_host(block_n, out_bytes) * out_bytes;
     const uint32_t a_stage = 128 * 128;
     const uint32_t b_stage = (block_n / cta_group) * 128;
     return 2 * d_stage + stages * (a_stage + b_stage) + (2 * stages + 4) * 8 + 16 + 1024;
@@ -69,7 +69,7 @@ Cand eval_common(const DgaTilingPlan& p, uint32_t cta, uint32_t bn) {
     const uint32_t k_elems = 128 / in_b;
     const uint32_t kb = ceil_div(p.k, k_elems);
     Cand c{cta, bn, 0, 0, 0, 1e30};
-    const uint32_t fixed = 2 * 128 * 32 * out_b + 1024 + 256;
+    const uint32_t fixed = 2 * 128 * epi_cols_host(bn, out_b) * out_b + 1024 + 256;
     c.stages = max_stages(128 * 128 + (bn / cta) * 128, fixed, hw.smemBytes, 12);
     if (c.stages < 2) return c;
     const uint32_t clusters = hw.smCount / cta;
@@ -185,7 +185,7 @@ int finalize_plan(DgaTilingPlan& p) {
         }
         p.m1 = static_cast<uint16_t>(128 * cta);
         p.k1 = static_cast<uint16_t>(128 / in_b);
-        const uint32_t fixed = 2 * 128 * 32 * out_b + 1024 + 256;
+        const uint32_t fixed = 2 * 128 * epi_cols_host(p.n1, out_b) * out_b + 1024 + 256;
         const uint32_t cap = max_stages(128 * 128 + (p.n1 / cta) * 128, fixed, hw.smemBytes, 12);
         if (p.stages == 0 || p.stages > cap) p.stages = static_cast<uint8_t>(cap);
         if (p.stages < 2) {

@@ -29,6 +29,8 @@ inline uint32_t elem_bytes(int32_t dtype) {
     return dtype == ACL_FLOAT ? 4u : dtype == ACL_FLOAT8_E4M3FN ? 1u : 2u;
 }
 
+// Columns per output store of the persistent kernel (mirrors epi_cols_for() in gemm_sm100.cuh).
+inline uint32_t epi_cols_host(uint32_t block_n, uint32_t out_bytes) { return (out_bytes == 2 && block_n % 64 == 0) ? 64u : 32u; }
 // Smem bytes the persistent kernel needs for a (block_n, stages) choice;
 // mirrors make_smem_layout() in gemm_sm100.cuh (+1 KB alignment slack).
 uint32_t common_smem_bytes(uint32_t block_n, uint32_t cta_group, uint32_t stages, uint32_t out_bytes,
