@@ -88,18 +88,28 @@ def run_ours(args, rank, world):
     sampler = B.ClockSampler(local)
     sampler.start()
     launches0 = dga.kernel_launch_count()
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
-    ev[0].record(stream)
+    # the timed region: exactly K steps between two events, nothing else on the stream (an event record between two
+    # launches would also break their programmatic-dependent-launch overlap)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
     for i in range(args.steps):
         step(i)
-        ev[i + 1].record(stream)
+    e1.record(stream)
     fence()
     clocks = sampler.finish()
     launches = dga.kernel_launch_count() - launches0
     if graph is not None:
         launches = args.steps * launches_per_step   # replays do not pass through the host counter
-    total_ms = ev[0].elapsed_time(ev[-1])
-    per_step = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps))
+    total_ms = e0.elapsed_time(e1)
+    # per-step spread (median / min), from a second pass with an event after every step; not the headline
+    n_probe = min(args.steps, 50)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(n_probe + 1)]
+    ev[0].record(stream)
+    for i in range(n_probe):
+        step(i)
+        ev[i + 1].record(stream)
+    fence()
+    per_step = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(n_probe))
     t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -109,7 +119,7 @@ def run_ours(args, rank, world):
     value = flops * n_launch * world / (total_ms_max * 1e-3) / 1e12
 
     # ---- e2e: host buffers in, host buffer out, through the public operator call
-    e2e = e2e_run(dga, dev, m, n, k, steps=max(3, min(args.steps, 10)), flops=flops, world=world, dist=dist, fp8=fp8)
+    e2e = e2e_run(dga, dev, m, n, k, steps=max(3, min(args.steps, 20)), flops=flops, world=world, dist=dist, fp8=fp8)
 
     # ---- optional: all-gather of C over NVLink (only when the caller needs the full output)
     gather = None
@@ -167,51 +177,81 @@ def run_ours(args, rank, world):
 
 
 def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False):
-    """Same metric end to end: pinned host A and W -> device, operator call, C -> pinned host, all inside the
-    timed region (CUDA events on the launching stream)."""
+    """Same metric end to end: every step copies its A and W from pinned host memory to the device, calls the
+    operator and copies C back to pinned host memory, all inside the timed region.  The three legs run on three
+    streams over a ring of 2 device buffer sets, so the copies of step i+1 and i-1 overlap the GEMM of step i
+    (PCIe is full duplex); every step still moves all of its own bytes."""
     in_dtype = torch.float8_e4m3fn if fp8 else torch.bfloat16
+    depth = 2
     ha = torch.randn((m, k)).to(in_dtype).pin_memory()
     hw = torch.randn((n, k)).to(in_dtype).pin_memory()
-    hc = torch.empty((m, n), dtype=torch.bfloat16).pin_memory()
-    da, dw = torch.empty_like(ha, device=dev), torch.empty_like(hw, device=dev)
-    dc = torch.empty((m, n), dtype=torch.bfloat16, device=dev)
+    hc = [torch.empty((m, n), dtype=torch.bfloat16).pin_memory() for _ in range(depth)]
+    da = [torch.empty_like(ha, device=dev) for _ in range(depth)]
+    dw = [torch.empty_like(hw, device=dev) for _ in range(depth)]
+    dc = [torch.empty((m, n), dtype=torch.bfloat16, device=dev) for _ in range(depth)]
     extra = 0
     if fp8:
         hsa = (torch.rand((m, -(-k // 128))) + 0.5).pin_memory()
         hsw = (torch.rand((-(-n // 128), -(-k // 128))) + 0.5).pin_memory()
-        dsa, dsw = torch.empty_like(hsa, device=dev), torch.empty_like(hsw, device=dev)
+        dsa = [torch.empty_like(hsa, device=dev) for _ in range(depth)]
+        dsw = [torch.empty_like(hsw, device=dev) for _ in range(depth)]
         extra = hsa.numel() * 4 + hsw.numel() * 4
-    stream = torch.cuda.current_stream()
+    main = torch.cuda.current_stream()
+    s_in, s_mm, s_out = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
+    in_done = [torch.cuda.Event() for _ in range(depth)]
+    mm_done = [torch.cuda.Event() for _ in range(depth)]
+    out_done = [torch.cuda.Event() for _ in range(depth)]
 
-    def one():
-        da.copy_(ha, non_blocking=True)
-        dw.copy_(hw, non_blocking=True)
-        if fp8:
-            dsa.copy_(hsa, non_blocking=True)
-            dsw.copy_(hsw, non_blocking=True)
-            dga.fp8_block_scaled_matmul(da, dsa, dw, dsw, out=dc)
-        else:
-            dga.catlass_dynamic_matmul(da, dw.t(), out=dc)     # two-phase C ABI underneath
-        hc.copy_(dc, non_blocking=True)
+    def one(j):
+        i = j % depth
+        with torch.cuda.stream(s_in):
+            s_in.wait_event(mm_done[i])          # the GEMM that last read this slot's inputs
+            da[i].copy_(ha, non_blocking=True)
+            dw[i].copy_(hw, non_blocking=True)
+            if fp8:
+                dsa[i].copy_(hsa, non_blocking=True)
+                dsw[i].copy_(hsw, non_blocking=True)
+            in_done[i].record(s_in)
+        with torch.cuda.stream(s_mm):
+            s_mm.wait_event(in_done[i])
+            s_mm.wait_event(out_done[i])         # the copy-out that last read this slot's C
+            if fp8:
+                dga.fp8_block_scaled_matmul(da[i], dsa[i], dw[i], dsw[i], out=dc[i])
+            else:
+                dga.catlass_dynamic_matmul(da[i], dw[i].t(), out=dc[i])     # two-phase C ABI underneath
+            mm_done[i].record(s_mm)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(mm_done[i])
+            hc[i].copy_(dc[i], non_blocking=True)
+            out_done[i].record(s_out)
 
-    for _ in range(3):
-        one()
+    def drain():
+        for st in (s_in, s_mm, s_out):
+            main.wait_stream(st)
+
+    for j in range(3):
+        one(j)
+    drain()
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for _ in range(steps):
-        one()
-    e1.record(stream)
+    e0.record(main)
+    for st in (s_in, s_mm, s_out):
+        st.wait_stream(main)
+    for j in range(steps):
+        one(j)
+    drain()
+    e1.record(main)
     torch.cuda.synchronize()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
     if dist is not None:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    checksum = float(hc.float().abs().mean())   # the device->host result is really read
+    checksum = float(sum(h.float().abs().mean() for h in hc) / depth)   # the device->host results are really read
     return {"value": flops * steps * world / (float(ms.item()) * 1e-3) / 1e12, "unit": "TFLOP/s",
-            "h2d_bytes_per_step": int((ha.numel() + hw.numel()) * ha.element_size() + extra), "d2h_bytes_per_step": int(hc.numel() * 2),
-            "steps": steps, "result_abs_mean": checksum}
+            "h2d_bytes_per_step": int((ha.numel() + hw.numel()) * ha.element_size() + extra),
+            "d2h_bytes_per_step": int(hc[0].numel() * 2), "steps": steps, "result_abs_mean": checksum,
+            "pipeline": "3 streams (H2D | GEMM | D2H) over %d buffer sets" % depth}
 
 
 def allgather_run(dist, dev, c_local, world):

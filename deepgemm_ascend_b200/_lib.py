@@ -79,6 +79,7 @@ SIGNATURES = {
     "dgaNShardMatmulGetWorkspaceSize": (_i32, [_P(AclTensor), _P(AclTensor), _P(_vp), _u32, _u32, ctypes.c_int64,
                                             ctypes.c_int64, _P(_u64), _P(_vp)]),
     "dgaNShardMatmul": (_i32, [_vp, _u64, _vp, _vp]),
+    "dgaSetOption": (_i32, [ctypes.c_char_p, ctypes.c_int64]),
     "dgaGetLastError": (ctypes.c_char_p, []),
     "dgaKernelLaunchCount": (_u64, []),
     "dgaVersion": (ctypes.c_char_p, []),

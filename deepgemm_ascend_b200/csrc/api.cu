@@ -18,11 +18,15 @@
 
 #include "gemm_smallm_sm100.cuh"
 #include "gemm_fp8_sm100.cuh"
+#include "repack_sm100.cuh"
 #include "tile_selector.h"
 
 namespace dga {
 
 static std::atomic<uint64_t> g_launches{0};
+// tuning knobs (dgaSetOption); -1 = built-in default
+static std::atomic<int64_t> g_opt_splitk_prefetch{-1};
+static std::atomic<int64_t> g_opt_pdl{-1};
 
 #define DGA_CUDA(expr)                                                                       \
     do {                                                                                     \
@@ -92,13 +96,36 @@ struct DenseLaunch {
     const void* b;
     void* d;
     uint64_t lda, ldb, ldd;  // elements
+    // What the GEMM kernel itself reads and writes: the caller's operands, or their repacked copies in the
+    // workspace when a padding tag is set (set by launch_dense on every call: the workspace may move).
+    struct Operands {
+        const void* a; const void* b; void* d;
+        uint64_t lda, ldb, ldd;
+    } eff{}, enc{};          // enc: what the tensor maps below were encoded for
     CUtensorMap tm_a, tm_b, tm_d;
     bool encoded = false;
+    bool maps_fresh() const { return encoded && std::memcmp(&eff, &enc, sizeof(Operands)) == 0; }
     // N-sharded execution: the column slice of every peer's C (device pointers mapped into this process)
     uint32_t num_peers = 0;
     void* peer_d[kMaxPeers] = {};
     PeerMaps peers{};
 };
+
+// Launch attributes shared by every tensor-core kernel: the cluster shape and programmatic dependent launch (the
+// kernels call griddepcontrol.wait before their first global access, so the prologue of launch i+1 overlaps the
+// tail of launch i on the same stream).  DGA_PDL=0 turns the second one off (A/B measurements).
+static void fill_launch_attrs(cudaLaunchConfig_t& cfg, cudaLaunchAttribute (&attr)[2], uint32_t cluster) {
+    static const bool pdl = [] { const char* e = std::getenv("DGA_PDL"); return e == nullptr || std::atoi(e) != 0; }();
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    const int64_t opt = g_opt_pdl.load(std::memory_order_relaxed);
+    cfg.numAttrs = (opt >= 0 ? opt != 0 : pdl) ? 2 : 1;
+}
 
 // cudaFuncSetAttribute costs microseconds of host time; remember the largest opt-in per kernel instance.
 template <typename K>
@@ -123,13 +150,8 @@ static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaSt
     cfg.blockDim = dim3(kNumThreads);
     cfg.dynamicSmemBytes = L.plan.smemBytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = kCta;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cudaLaunchAttribute attr[2];
+    fill_launch_attrs(cfg, attr, kCta);
     DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, L.tm_a, L.tm_b, L.peers, gp));  // no scale maps here
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
@@ -149,12 +171,12 @@ static int launch_common_out(const DenseLaunch& L, const GemmParams& gp, cudaStr
 static int encode_common(DenseLaunch& L) {
     const DgaTilingPlan& p = L.plan;
     const uint32_t cta = p.ctaGroup, load_n = p.n1 / cta;
-    int rc = make_tmap_2d(&L.tm_a, L.a, p.dtype, p.k, p.m, L.lda, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+    int rc = make_tmap_2d(&L.tm_a, L.eff.a, p.dtype, p.k, p.m, L.eff.lda, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != ACLNN_SUCCESS) return rc;
     if (p.layoutTagB == 1)  // weight stored [N, K]
-        rc = make_tmap_2d(&L.tm_b, L.b, p.dtype, p.k, p.n, L.ldb, 64, load_n, CU_TENSOR_MAP_SWIZZLE_128B);
+        rc = make_tmap_2d(&L.tm_b, L.eff.b, p.dtype, p.k, p.n, L.eff.ldb, 64, load_n, CU_TENSOR_MAP_SWIZZLE_128B);
     else  // row-major [K, N]: boxes of 64 columns x 64 k-rows
-        rc = make_tmap_2d(&L.tm_b, L.b, p.dtype, p.n, p.k, L.ldb, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+        rc = make_tmap_2d(&L.tm_b, L.eff.b, p.dtype, p.n, p.k, L.eff.ldb, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != ACLNN_SUCCESS) return rc;
     const uint32_t epi = epi_cols_for(p.n1, elem_bytes(p.outDtype));
     const bool wide = epi * elem_bytes(p.outDtype) == 128;
@@ -163,15 +185,16 @@ static int encode_common(DenseLaunch& L) {
         rc = make_tmap_2d(&L.peers.m[i], L.peer_d[i], p.outDtype, p.n, p.m, L.ldd, epi, 128, d_swz);
         if (rc != ACLNN_SUCCESS) return rc;
     }
-    return make_tmap_2d(&L.tm_d, L.d, p.outDtype, p.n, p.m, L.ldd, epi, 128, d_swz);
+    return make_tmap_2d(&L.tm_d, L.eff.d, p.outDtype, p.n, p.m, L.eff.ldd, epi, 128, d_swz);
 }
 
 static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     const DgaTilingPlan& p = L.plan;
-    if (!L.encoded) {
+    if (!L.maps_fresh()) {
         int rc = encode_common(L);
         if (rc != ACLNN_SUCCESS) return rc;
         L.encoded = true;
+        L.enc = L.eff;
     }
     const uint32_t cta = p.ctaGroup;
     GemmParams gp{};
@@ -230,13 +253,8 @@ static int launch_splitk_inst(const DenseLaunch& L, const SmallMParams& sp, cuda
     cfg.blockDim = dim3(kNumThreads);
     cfg.dynamicSmemBytes = L.plan.smemBytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = sp.split;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cudaLaunchAttribute attr[2];
+    fill_launch_attrs(cfg, attr, sp.split);
     DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, sp));
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
@@ -245,13 +263,14 @@ static int launch_splitk_inst(const DenseLaunch& L, const SmallMParams& sp, cuda
 static int launch_splitk(DenseLaunch& L, cudaStream_t stream) {
     const DgaTilingPlan& p = L.plan;
     const uint32_t m_pad = p.m1;
-    if (!L.encoded) {
+    if (!L.maps_fresh()) {
         // tm_a slot holds the weight map (UMMA A operand), tm_b the activation map (UMMA B operand)
-        int rc = make_tmap_2d(&L.tm_a, L.b, p.dtype, p.k, p.n, L.ldb, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+        int rc = make_tmap_2d(&L.tm_a, L.eff.b, p.dtype, p.k, p.n, L.eff.ldb, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc != ACLNN_SUCCESS) return rc;
-        rc = make_tmap_2d(&L.tm_b, L.a, p.dtype, p.k, p.m, L.lda, 64, m_pad, CU_TENSOR_MAP_SWIZZLE_128B);
+        rc = make_tmap_2d(&L.tm_b, L.eff.a, p.dtype, p.k, p.m, L.eff.lda, 64, m_pad, CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc != ACLNN_SUCCESS) return rc;
         L.encoded = true;
+        L.enc = L.eff;
     }
     SmallMParams sp{};
     sp.m = p.m; sp.n = p.n; sp.k = p.k;
@@ -259,12 +278,14 @@ static int launch_splitk(DenseLaunch& L, cudaStream_t stream) {
     sp.split = p.splitkFactor;
     sp.num_stages = p.stages;
     sp.k_blocks = ceil_div(p.k, 64);
-    sp.ldc = static_cast<uint32_t>(L.ldd);
+    sp.ldc = static_cast<uint32_t>(L.eff.ldd);
     sp.idesc = make_idesc(128, m_pad, p.dtype == ACL_BF16 ? 1u : 0u, 0, 0);
     uint32_t cols = 32;
     while (cols < m_pad) cols <<= 1;
     sp.tmem_cols = cols;
-    sp.out = L.d;
+    const int64_t pf = g_opt_splitk_prefetch.load(std::memory_order_relaxed);
+    sp.prefetch_kb = pf >= 0 ? uint32_t(pf) : 8u;
+    sp.out = L.eff.d;
     if (sp.k_blocks < sp.split || uint64_t(p.stages) * (16384 + m_pad * 128) < uint64_t(m_pad) * 512) {
         set_error("split-K plan infeasible for this shape");
         return ACLNN_ERR_INNER_TILING_ERROR;
@@ -278,10 +299,11 @@ static int launch_splitk(DenseLaunch& L, cudaStream_t stream) {
     return ACLNN_ERR_PARAM_INVALID;
 }
 
-static int launch_dense(DenseLaunch& L, cudaStream_t stream, void* workspace = nullptr) {
+static int launch_variant(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     switch (L.plan.kernelSerial) {
         case DGA_KERNEL_COMMON:
-        case DGA_KERNEL_SMALL: return launch_common(L, stream, nullptr);
+        case DGA_KERNEL_SMALL:
+        case DGA_KERNEL_PADDING_COMMON: return launch_common(L, stream, nullptr);
         case DGA_KERNEL_STREAMK:
             if (workspace == nullptr) {
                 set_error("the stream-K variant needs its workspace");
@@ -292,6 +314,74 @@ static int launch_dense(DenseLaunch& L, cudaStream_t stream, void* workspace = n
     }
     set_error("kernel variant " + std::to_string(int(L.plan.kernelSerial)) + " is not built");
     return ACLNN_ERR_INNER_TILING_ERROR;
+}
+
+// rows x cols elements of `eb` bytes from a pitch of src_ld to a pitch of dst_ld (elements)
+static int launch_repack(const void* src, uint64_t src_ld, void* dst, uint64_t dst_ld, uint32_t rows, uint32_t cols,
+                         uint32_t eb, cudaStream_t stream) {
+    const dim3 grid(ceil_div(cols, kRepackThreads), ceil_div(rows, kRepackRows));
+    if (eb == 4)
+        repack_rows_kernel<uint32_t><<<grid, kRepackThreads, 0, stream>>>(
+            static_cast<const uint32_t*>(src), src_ld, static_cast<uint32_t*>(dst), dst_ld, rows, cols);
+    else
+        repack_rows_kernel<uint16_t><<<grid, kRepackThreads, 0, stream>>>(
+            static_cast<const uint16_t*>(src), src_ld, static_cast<uint16_t*>(dst), dst_ld, rows, cols);
+    DGA_CUDA(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return ACLNN_SUCCESS;
+}
+
+// Padding tags from the operands the caller actually passed (role of GetPaddingTag, select_kernel.cpp:82-268, cut
+// down to the one thing that matters on B200): TMA cannot address a tensor whose base or row pitch is not a
+// multiple of 16 bytes, so exactly those operands go through the workspace.  Re-derives workspace bytes.
+static int apply_padding(DenseLaunch& L, bool allow_repack = true) {
+    DgaTilingPlan& p = L.plan;
+    const uint32_t ib = elem_bytes(p.dtype), ob = elem_bytes(p.outDtype);
+    auto unaligned = [](const void* ptr, uint64_t ld, uint32_t eb) {
+        return (reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || (ld * eb) % 16 != 0;
+    };
+    p.strideA = L.lda; p.strideB = L.ldb; p.strideC = L.ldd;
+    p.paddingTagA = unaligned(L.a, L.lda, ib) ? 1 : 0;
+    p.paddingTagB = unaligned(L.b, L.ldb, ib) ? 1 : 0;
+    p.paddingTagC = unaligned(L.d, L.ldd, ob) ? 1 : 0;
+    if (!allow_repack && (p.paddingTagA || p.paddingTagB || p.paddingTagC)) {
+        set_error("base pointers and leading dimensions must be 16-byte aligned on this entry point");
+        return ACLNN_ERR_INNER_TILING_ERROR;
+    }
+    return finalize_plan(p);
+}
+
+static int launch_dense(DenseLaunch& L, cudaStream_t stream, void* workspace = nullptr) {
+    const DgaTilingPlan& p = L.plan;
+    L.eff = {L.a, L.b, L.d, L.lda, L.ldb, L.ldd};
+    if (!(p.paddingTagA || p.paddingTagB || p.paddingTagC)) return launch_variant(L, stream, workspace);
+    if (workspace == nullptr) {
+        set_error("unaligned operands are repacked through the workspace, which is missing");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    // PaddingCommon (padding_common_matmul_kernel.h:33-107): repack -> GEMM on the aligned copies -> copy C back
+    const PadLayout pl = pad_layout(p);
+    char* ws = static_cast<char*>(workspace);
+    const uint32_t ib = elem_bytes(p.dtype), ob = elem_bytes(p.outDtype);
+    int rc = ACLNN_SUCCESS;
+    if (p.paddingTagA) {
+        rc = launch_repack(L.a, L.lda, ws + pl.offA, pl.ldA, p.m, p.k, ib, stream);
+        if (rc != ACLNN_SUCCESS) return rc;
+        L.eff.a = ws + pl.offA; L.eff.lda = pl.ldA;
+    }
+    if (p.paddingTagB) {
+        const uint32_t rows = p.layoutTagB ? p.n : p.k, cols = p.layoutTagB ? p.k : p.n;
+        rc = launch_repack(L.b, L.ldb, ws + pl.offB, pl.ldB, rows, cols, ib, stream);
+        if (rc != ACLNN_SUCCESS) return rc;
+        L.eff.b = ws + pl.offB; L.eff.ldb = pl.ldB;
+    }
+    if (p.paddingTagC) {
+        L.eff.d = ws + pl.offC; L.eff.ldd = pl.ldC;
+    }
+    rc = launch_variant(L, stream, ws + pl.bytes);
+    if (rc != ACLNN_SUCCESS) return rc;
+    if (p.paddingTagC) rc = launch_repack(ws + pl.offC, pl.ldC, L.d, L.ldd, p.m, p.n, ob, stream);
+    return rc;
 }
 
 // ---- fp8 e4m3 block-scaled -------------------------------------------------------------------------------
@@ -422,13 +512,8 @@ static int launch_fp8_inst(const Fp8Launch& L, const Fp8Params& fp, cudaStream_t
     cfg.blockDim = dim3(kFp8Threads);
     cfg.dynamicSmemBytes = L.smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = kCta;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cudaLaunchAttribute attr[2];
+    fill_launch_attrs(cfg, attr, kCta);
     DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, fp));
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
@@ -444,13 +529,8 @@ static int launch_mx_inst(const Fp8Launch& L, const GemmParams& gp, cudaStream_t
     cfg.blockDim = dim3(kNumThreads);
     cfg.dynamicSmemBytes = L.mx_smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = kCta;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cudaLaunchAttribute attr[2];
+    fill_launch_attrs(cfg, attr, kCta);
     static const PeerMaps no_peers{};
     DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b_mx, L.tm_d_mx, L.tm_sfa, L.tm_sfb, no_peers, gp));
     g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -654,15 +734,6 @@ static aclnnStatus validate_dense(const aclTensor* self, const aclTensor* mat2, 
     return ACLNN_SUCCESS;
 }
 
-static aclnnStatus check_strides(const DenseLaunch& L) {
-    const uint32_t ib = elem_bytes(L.plan.dtype), ob = elem_bytes(L.plan.outDtype);
-    if ((L.lda * ib) % 16 || (L.ldb * ib) % 16 || (L.ldd * ob) % 16) {
-        set_error("leading dimensions must be 16-byte aligned (stride repack not built yet)");
-        return ACLNN_ERR_INNER_TILING_ERROR;
-    }
-    return ACLNN_SUCCESS;
-}
-
 aclnnStatus aclnnCatlassDynamicMatmulGetWorkspaceSize(const aclTensor* self, const aclTensor* mat2,
                                                       const aclTensor* out, uint64_t* workspaceSize,
                                                       aclOpExecutor** executor) {
@@ -673,7 +744,7 @@ aclnnStatus aclnnCatlassDynamicMatmulGetWorkspaceSize(const aclTensor* self, con
     aclOpExecutor* ex = new aclOpExecutor{};
     aclnnStatus rc = validate_dense(self, mat2, out, ex->dense);
     if (rc == ACLNN_SUCCESS) rc = select_kernel_with_cache(ex->dense.plan);
-    if (rc == ACLNN_SUCCESS) rc = check_strides(ex->dense);
+    if (rc == ACLNN_SUCCESS) rc = apply_padding(ex->dense);
     if (rc != ACLNN_SUCCESS) {
         delete ex;
         return rc;
@@ -721,11 +792,10 @@ aclnnStatus dgaMatmulWithPlan(const aclTensor* self, const aclTensor* mat2, cons
     // shape, dtype and layout always come from the tensors
     p.m = L.plan.m; p.n = L.plan.n; p.k = L.plan.k;
     p.dtype = L.plan.dtype; p.outDtype = L.plan.outDtype; p.layoutTagB = L.plan.layoutTagB;
-    rc = finalize_plan(p);
-    if (rc != ACLNN_SUCCESS) return rc;
     L.plan = p;
-    rc = check_strides(L);
+    rc = apply_padding(L);   // also finalises the plan
     if (rc != ACLNN_SUCCESS) return rc;
+    p = L.plan;
     if (workspaceSize < p.workspaceBytes) {
         set_error("workspace too small: the plan needs " + std::to_string(p.workspaceBytes) + " bytes");
         return ACLNN_ERR_PARAM_INVALID;
@@ -779,7 +849,7 @@ aclnnStatus dgaNShardMatmulGetWorkspaceSize(const aclTensor* self, const aclTens
             if (rc == ACLNN_SUCCESS) { q.strideA = p.strideA; q.strideB = p.strideB; q.strideC = p.strideC; p = q; }
         }
     }
-    if (rc == ACLNN_SUCCESS) rc = check_strides(ex->dense);
+    if (rc == ACLNN_SUCCESS) rc = apply_padding(ex->dense, /*allow_repack=*/false);
     if (rc != ACLNN_SUCCESS) {
         delete ex;
         return rc;
@@ -947,7 +1017,17 @@ static aclnnStatus framework_gemm(const void* x, const void* y, void* z, uint32_
     if (rc != ACLNN_SUCCESS) return rc;
     L.a = x; L.b = y; L.d = z;
     L.lda = k; L.ldb = n; L.ldd = n;
-    return launch_dense(L, stream);
+    // stream-K keeps arrival counters in a caller-owned workspace across launches; with scratch that comes and
+    // goes per call (below) a tuned-table row asking for it falls back to the plain persistent walk
+    if (L.plan.kernelSerial == DGA_KERNEL_STREAMK) L.plan.kernelSerial = DGA_KERNEL_COMMON;
+    rc = apply_padding(L);   // the reference's kernel takes any (m, n, k): odd n or k go through a repack
+    if (rc != ACLNN_SUCCESS) return rc;
+    // the framework entry points have no workspace argument (python_api.cpp:13-35): stream-ordered scratch
+    void* ws = nullptr;
+    if (L.plan.workspaceBytes != 0) DGA_CUDA(cudaMallocAsync(&ws, L.plan.workspaceBytes, stream));
+    rc = launch_dense(L, stream, ws);
+    if (ws != nullptr) cudaFreeAsync(ws, stream);
+    return rc;
 }
 
 aclnnStatus dgaRunMmadRtc(const void* x, const void* y, void* z, uint32_t batch, uint32_t m, uint32_t n, uint32_t k,
@@ -1037,6 +1117,16 @@ aclnnStatus dgaNShardRange(uint32_t n, uint32_t worldSize, uint32_t rank, uint32
 }
 
 // ---- misc --------------------------------------------------------------------------------------------------
+aclnnStatus dgaSetOption(const char* name, int64_t value) {
+    if (name == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    if (std::strcmp(name, "splitk_prefetch_kb") == 0) g_opt_splitk_prefetch.store(value);
+    else if (std::strcmp(name, "pdl") == 0) g_opt_pdl.store(value);
+    else {
+        set_error(std::string("unknown option ") + name);
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    return ACLNN_SUCCESS;
+}
 const char* dgaGetLastError(void) { return last_error(); }
 uint64_t dgaKernelLaunchCount(void) { return g_launches.load(); }
 const char* dgaVersion(void) { return "dga-b200 0.1 (sm_100a)"; }

@@ -71,7 +71,11 @@ __global__ void __launch_bounds__(kFp8Threads, 1)
 gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                       const __grid_constant__ CUtensorMap tm_d, const Fp8Params p) {
     static_assert(kBN % 32 == 0 && kBN <= 256 && kBN % (16 * kCta) == 0, "unsupported block_n");
-    if (p.gate != nullptr && *p.gate != p.gate_expect) return;   // grid-uniform
+    ptx::grid_dep_launch();
+    if (p.gate != nullptr) {
+        ptx::grid_dep_wait();     // the flag was written by a previous grid
+        if (*p.gate != p.gate_expect) return;   // grid-uniform
+    }
     constexpr uint32_t kChunks = kBN / 32;
     constexpr uint32_t kOwned = (kChunks + 1) / 2;   // chunks per warp group (group 1 may own one less)
     constexpr uint32_t kTmemCols = (2 * kBN <= 32) ? 32 : (2 * kBN <= 64) ? 64 : (2 * kBN <= 128) ? 128
@@ -121,6 +125,7 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
     if constexpr (kCta == 2) ptx::cluster_sync(); else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
+    ptx::grid_dep_wait();
     constexpr uint32_t kLoadN = kBN / kCta;
 
     if (warp < 4) {

@@ -225,7 +225,11 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                   const __grid_constant__ CUtensorMap tm_sfb, const __grid_constant__ PeerMaps peers,
                   const GemmParams p) {
     static_assert(!(kMx && kBMn), "block-scaled fp8 wants K-major operands");
-    if (p.gate != nullptr && *p.gate != p.gate_expect) return;   // grid-uniform
+    ptx::grid_dep_launch();   // the next grid on the stream may set itself up while this one runs
+    if (p.gate != nullptr) {
+        ptx::grid_dep_wait();     // the flag was written by the previous grid
+        if (*p.gate != p.gate_expect) return;   // grid-uniform
+    }
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
@@ -273,6 +277,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     if constexpr (kCta == 2) ptx::cluster_sync(); else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
+    ptx::grid_dep_wait();   // first global access (TMA loads, stores, stream-K workspace) comes after this
 
     const uint32_t load_n = p.block_n / kCta;  // B rows this CTA loads per stage
 

@@ -27,6 +27,7 @@ struct SmallMParams {
     uint32_t ldc;        // elements
     uint32_t idesc;
     uint32_t tmem_cols;  // power of two >= max(32, m_pad)
+    uint32_t prefetch_kb; // K blocks of this CTA's weight slice pulled into L2 before the grid-dependency wait
     void* out;
 };
 
@@ -57,12 +58,13 @@ __device__ __forceinline__ void store_out(OutT* p, float v) {
 }
 
 template <typename OutT>
-__global__ void __launch_bounds__(kNumThreads, 1)
+__global__ void __launch_bounds__(kNumThreads, 2)
 gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
                          const SmallMParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
+    ptx::grid_dep_launch();
 
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lane = threadIdx.x & 31;
@@ -84,6 +86,12 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tensormap(&tm_w);
         ptx::prefetch_tensormap(&tm_x);
+        // Back-to-back launches (decode: one GEMM after another): this grid becomes resident while its
+        // predecessor is still draining, and HBM would sit idle through that tail and through our own first
+        // round trip.  Pull the head of our weight slice into L2 now; the real loads below hit it there.
+        const uint32_t pf = min(p.prefetch_kb, kb1 - kb0);
+        for (uint32_t i = 0; i < pf; ++i)
+            ptx::tma_prefetch_2d(&tm_w, static_cast<int32_t>((kb0 + i) * 64), static_cast<int32_t>(n0));
     }
     if (warp == 1 && lane == 0) {
         for (uint32_t s = 0; s < stages; ++s) {
@@ -98,6 +106,7 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
+    ptx::grid_dep_wait();   // the predecessor on the stream may still have been running up to here
 
     if (warp == 0) {
         if (lane == 0) {

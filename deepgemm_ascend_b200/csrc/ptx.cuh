@@ -46,6 +46,14 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+// ------------------------------------------- programmatic dependent launch
+// Launched with cudaLaunchAttributeProgrammaticStreamSerialization, a grid may start while its predecessor on
+// the stream is still draining: everything up to grid_dep_wait() (barrier init, TMEM allocation, descriptor
+// prefetch) overlaps the predecessor's tail.  grid_dep_wait() returns once the predecessor has completed and
+// its memory is visible, so it must precede the first global access on every path; both are no-ops otherwise.
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ----------------------------------------------------------------- cluster
 __device__ __forceinline__ void cluster_arrive() {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
@@ -164,6 +172,12 @@ __device__ __forceinline__ void tma_load_3d(const void* desc, uint64_t* bar, voi
         " [%0], [%1, {%3, %4, %5}], [%2], %6;"
         :: "r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(desc)), "r"(smem_u32(bar)),
            "r"(c0), "r"(c1), "r"(c2), "l"(hint) : "memory");
+}
+// L2 prefetch of one box: warms the (device-coherent) L2 only, no shared-memory destination and no completion
+// to wait for, so it may be issued for data another grid is still producing.
+__device__ __forceinline__ void tma_prefetch_2d(const void* desc, int32_t c0, int32_t c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];"
+                 :: "l"(reinterpret_cast<uint64_t>(desc)), "r"(c0), "r"(c1) : "memory");
 }
 __device__ __forceinline__ void tma_store_2d(const void* desc, const void* smem, int32_t c0, int32_t c1) {
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"

@@ -158,9 +158,30 @@ uint64_t streamk_partial_bytes(uint32_t clusters, uint32_t cta_group, uint32_t b
     return uint64_t(clusters) * 2 * cta_group * 128 * block_n * 4;
 }
 
+PadLayout pad_layout(const DgaTilingPlan& p) {
+    const uint64_t in_b = elem_bytes(p.dtype), out_b = elem_bytes(p.outDtype);
+    auto pitch = [](uint64_t cols) { return (cols + 63) / 64 * 64; };
+    auto region = [](uint64_t b) { return (b + 1023) & ~1023ull; };
+    PadLayout l{};
+    l.ldA = pitch(p.k);
+    l.ldB = pitch(p.layoutTagB ? p.k : p.n);
+    l.ldC = pitch(p.n);
+    uint64_t off = 0;
+    l.offA = off;
+    if (p.paddingTagA) off += region(uint64_t(p.m) * l.ldA * in_b);
+    l.offB = off;
+    if (p.paddingTagB) off += region(uint64_t(p.layoutTagB ? p.n : p.k) * l.ldB * in_b);
+    l.offC = off;
+    if (p.paddingTagC) off += region(uint64_t(p.m) * l.ldC * out_b);
+    l.bytes = off;
+    return l;
+}
+
 int finalize_plan(DgaTilingPlan& p) {
     const PlatformInfo& hw = platform();
     const uint32_t in_b = elem_bytes(p.dtype), out_b = elem_bytes(p.outDtype);
+    // PaddingCommon is Common behind a repack: the tags say what is repacked, the tile fields mean the same
+    if (p.kernelSerial == DGA_KERNEL_PADDING_COMMON) p.kernelSerial = DGA_KERNEL_COMMON;
     if (p.kernelSerial == DGA_KERNEL_SPLITK) {
         const uint32_t m_pad = round_up(p.m, 16);
         if (m_pad > 256 || p.layoutTagB != 1 || in_b != 2) {
@@ -176,6 +197,7 @@ int finalize_plan(DgaTilingPlan& p) {
         p.blockDim = ceil_div(p.n, 128) * p.splitkFactor;
         p.smemBytes = splitk_smem_bytes(m_pad, p.stages);
         p.workspaceBytes = 0;
+        p.paddingTagC = 0;   // this kernel stores C with plain st.global: any pitch will do
     } else {
         if (p.ctaGroup != 1 && p.ctaGroup != 2) p.ctaGroup = 2;
         const uint32_t cta = p.ctaGroup;
@@ -215,6 +237,12 @@ int finalize_plan(DgaTilingPlan& p) {
         if (p.splitkFactor == 0) p.splitkFactor = 1;
     }
     if (p.swizzleOffset == 0) p.swizzleOffset = 8;
+    if (p.paddingTagA || p.paddingTagB || p.paddingTagC) {
+        // repack region first, the variant's own workspace behind it (padding_common_matmul_kernel.h:77-82)
+        p.workspaceBytes += pad_layout(p).bytes;
+        if (p.kernelSerial == DGA_KERNEL_COMMON || p.kernelSerial == DGA_KERNEL_SMALL)
+            p.kernelSerial = DGA_KERNEL_PADDING_COMMON;
+    }
     return ACLNN_SUCCESS;
 }
 
@@ -275,11 +303,8 @@ int select_kernel(DgaTilingPlan& p) {
     } else {
         fill_common(p, best);
     }
-    if (p.paddingTagA || p.paddingTagB || p.paddingTagC) {
-        // PaddingCommon survives only as a leading-dimension repack (padding_common_matmul_kernel.h:64-82)
-        set_error("leading dimension is not 16-byte aligned; stride repack (PADDING_ND) is not built yet");
-        return ACLNN_ERR_INNER_TILING_ERROR;
-    }
+    // PaddingCommon survives only as a leading-dimension repack (padding_common_matmul_kernel.h:64-82): the tags
+    // above describe contiguous operands; the launch path re-derives them from the caller's actual strides.
     return finalize_plan(p);
 }
 

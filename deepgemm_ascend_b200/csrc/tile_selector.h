@@ -51,6 +51,17 @@ void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t& dp,
 // Workspace layout of the stream-K variant: fp32 partial slots, then the per-tile arrival counters.
 uint64_t streamk_partial_bytes(uint32_t clusters, uint32_t cta_group, uint32_t block_n);
 
+// Stride repack (role of PaddingWorkspaceSize, op_kernel/kernel/kernel_utils.h:63-75, and of the workspace carve-up
+// padA | padB | padC in padding_common_matmul_kernel.h:77-82): operands whose paddingTag is set are copied to the
+// front of the workspace with a 128-byte-multiple row pitch; whatever else the variant needs (stream-K partials)
+// follows at `bytes`.  Pure function of (m, n, k, dtypes, layoutTagB, padding tags).
+struct PadLayout {
+    uint64_t ldA, ldB, ldC;      // padded leading dimensions, elements
+    uint64_t offA, offB, offC;   // byte offsets in the workspace
+    uint64_t bytes;              // total bytes of the repack region (0 when no tag is set), 1 KB granular
+};
+PadLayout pad_layout(const DgaTilingPlan& plan);
+
 // plan_cache.cpp
 int cache_get(DgaTilingPlan& plan);  // keyed by (m, n, k, dtype, outDtype, layoutTagB) already set in `plan`
 int cache_set(const DgaTilingPlan& plan);

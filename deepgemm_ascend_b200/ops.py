@@ -141,6 +141,11 @@ def matmul_with_plan(self, mat2, out, stream=None, **fields):
 _PLAN_WS = None
 
 
+def set_option(name, value):
+    """Process-wide tuning knob (see dgaSetOption in include/dga_b200.h); value < 0 restores the default."""
+    check(lib.dgaSetOption(name.encode(), int(value)), "dgaSetOption")
+
+
 def kernel_launch_count():
     return int(lib.dgaKernelLaunchCount())
 

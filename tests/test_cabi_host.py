@@ -91,9 +91,15 @@ def test_selector_invariants_on_reference_shapes(dga, golden_dir):
     shapes = sorted({tuple(r[:3]) for r in ref["cores24"]})
     assert len(shapes) >= 30
     for m, n, k in shapes:
-        if (k * 2) % 16 or (n * 2) % 16:
-            continue  # unaligned leading dimensions take the repack path, tested separately
         p = dga.select_kernel(m, n, k)
+        if (k * 2) % 16 or (n * 2) % 16:
+            # unaligned leading dimensions: repack through the workspace (PADDING_ND, tiling_params.h:24-29)
+            assert p["paddingTagA"] == p["paddingTagB"] == (1 if (k * 2) % 16 else 0)
+            assert p["paddingTagC"] == (1 if (n * 2) % 16 and p["kernelSerial"] != 3 else 0)
+            if p["paddingTagA"] or p["paddingTagB"] or p["paddingTagC"]:
+                assert p["kernelSerial"] in (2, 3, 4) and p["workspaceBytes"] > 0
+        else:
+            assert p["paddingTagA"] == p["paddingTagB"] == p["paddingTagC"] == 0
         # the invariants select_kernel_test.cpp:29-144 and do_tiling_test.cpp:29-153 assert
         assert p["m1"] > 0 and p["n1"] > 0 and p["k1"] > 0 and p["blockDim"] > 0
         assert p["blockDim"] <= 148 or p["kernelSerial"] == 3
@@ -101,6 +107,25 @@ def test_selector_invariants_on_reference_shapes(dga, golden_dir):
         assert p["stages"] >= 2
         assert p["strideA"] == k and p["strideB"] == k and p["strideC"] == n   # tiling_params.h:45-65
         assert p["swizzleDirection"] == (0 if m > n else 1)                     # tiling_params.h:64
+
+
+def test_padding_workspace_layout(dga):
+    """padA | padB | padC at the front of the workspace (padding_common_matmul_kernel.h:77-82), 128-byte row pitch."""
+    m, n, k = 300, 1001, 515
+    p = dga.select_kernel(m, n, k)
+    assert (p["paddingTagA"], p["paddingTagB"], p["paddingTagC"]) == (1, 1, 1) and p["kernelSerial"] == 2
+    kp, np_ = -(-k // 64) * 64, -(-n // 64) * 64
+    up = lambda b: (b + 1023) // 1024 * 1024  # noqa: E731
+    assert p["workspaceBytes"] == up(m * kp * 2) + up(n * kp * 2) + up(m * np_ * 2)
+    # aligned K, odd N: only C goes through the workspace (weight stored [N,K]) ...
+    q = dga.select_kernel(300, 1001, 512)
+    assert (q["paddingTagA"], q["paddingTagB"], q["paddingTagC"]) == (0, 0, 1)
+    # ... and with a row-major [K,N] weight its pitch is N as well
+    q = dga.select_kernel(300, 1001, 512, layout_b=0)
+    assert (q["paddingTagA"], q["paddingTagB"], q["paddingTagC"]) == (0, 1, 1)
+    # the decode kernel stores C directly: no C repack
+    q = dga.select_kernel(16, 1001, 512)
+    assert q["kernelSerial"] == 3 and q["paddingTagC"] == 0 and q["workspaceBytes"] == 0
 
 
 def test_selector_decision_structure(dga):

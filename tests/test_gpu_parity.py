@@ -123,8 +123,6 @@ def test_golden_vectors_framework_path(dga, golden_dir):
         x1, x2, golden = z[tag + "_x1"], z[tag + "_x2"], z[tag + "_golden"]
         m, k = x1.shape
         n = x2.shape[1]
-        if (n * 2) % 16 or (k * 2) % 16:
-            continue  # unaligned leading dimension: covered by the repack tests
         x = torch.from_numpy(x1).to(DEV)
         y = torch.from_numpy(x2).to(DEV)
         out = torch.zeros((m, n), dtype=torch.float32, device=DEV)
@@ -203,3 +201,57 @@ def test_strided_views_are_not_copied(dga):
     got = big_c[:, :384].float().cpu().numpy()
     assert orc.max_rel_err(got, orc.golden_fp64(a, b)) <= 2.0 ** -7
     assert float(big_c[:, 384:].abs().max()) == 0.0   # nothing written outside the view
+
+
+# ---- stride repack (role of PaddingCommonMatmulKernel / PADDING_ND, padding_common_matmul_kernel.h:33-107) ----------
+PADDING_CASES = [
+    # (m, n, k, dtype, layout_b, plan): leading dimensions that are not multiples of 16 bytes
+    (16, 578, 2014, torch.float16, 1, {}),                    # the custom_catlass demo shape as it is
+    (127, 509, 251, torch.bfloat16, 1, {}),
+    (127, 509, 251, torch.bfloat16, 0, {}),
+    (33, 77, 130, torch.float16, 0, {}),
+    (300, 1001, 515, torch.bfloat16, 1, {"kernelSerial": 0, "ctaGroup": 2, "n1": 128}),
+    (300, 1001, 515, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 1, "n1": 64}),   # PaddingStreamk
+    (1, 4097, 1027, torch.bfloat16, 1, {}),
+    (1279, 5003, 1537, torch.bfloat16, 1, {}),                # benchmark.py:41-43 class of odd shapes (K cut for the oracle)
+]
+
+
+@pytest.mark.parametrize("m,n,k,dtype,layout_b,plan", PADDING_CASES)
+def test_unaligned_leading_dimensions_take_the_repack_path(dga, m, n, k, dtype, layout_b, plan):
+    if not plan:
+        p = dga.select_kernel(m, n, k, dtype=dtype, layout_b=layout_b)
+        assert p["paddingTagA"] or p["paddingTagB"] or p["paddingTagC"]
+        assert p["workspaceBytes"] > 0
+    a, b = _inputs(m, n, k, dtype, seed=m + n + k)
+    got = _run_aclnn(dga, a, b, dtype, layout_b, **plan)
+    err = orc.max_rel_err(got, orc.golden_fp64(a, b))
+    assert err <= (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7), "max rel err %.3e" % err
+
+
+def test_misaligned_base_pointers_are_repacked(dga):
+    """A view that starts 2 bytes into an allocation: aligned pitch, unaligned base."""
+    m, n, k = 96, 200, 136
+    a, b = _inputs(m, n, k, torch.bfloat16, seed=11)
+    flat_a = torch.zeros(m * k + 8, dtype=torch.bfloat16, device=DEV)
+    flat_w = torch.zeros(n * k + 8, dtype=torch.bfloat16, device=DEV)
+    flat_c = torch.zeros(m * n + 8, dtype=torch.bfloat16, device=DEV)
+    va = flat_a[1:1 + m * k].view(m, k); va.copy_(_to_dev(a, torch.bfloat16))
+    vw = flat_w[3:3 + n * k].view(n, k); vw.copy_(_to_dev(b.T, torch.bfloat16))
+    vc = flat_c[5:5 + m * n].view(m, n)
+    dga.catlass_dynamic_matmul(va, vw.t(), out=vc)
+    torch.cuda.synchronize()
+    assert orc.max_rel_err(vc.float().cpu().numpy(), orc.golden_fp64(a, b)) <= 2.0 ** -7
+    assert float(flat_c[:5].abs().max()) == 0.0 and float(flat_c[5 + m * n:].abs().max()) == 0.0
+
+
+def test_framework_path_odd_shapes(dga):
+    """run_mmad_bench takes any (m, n, k) (benchmark.py:41-43 sweeps odd ones): fp16 -> fp32 with odd n and k."""
+    for m, n, k in ((48, 130, 321), (1, 77, 33), (257, 1003, 514)):
+        x1, x2, golden = orc.gen_golden_data(m, n, k, np.random.RandomState(m + n + k))
+        z = torch.zeros((m, n), dtype=torch.float32, device=DEV)
+        params = torch.tensor([1, 1, 4, 4, 8, 4] + [0] * 22, dtype=torch.int32, device=DEV)
+        dga.run_mmad_bench(torch.from_numpy(x1).to(DEV), torch.from_numpy(x2).to(DEV), z, params)
+        ok, ratio = orc.verify_result(z.cpu().numpy(), golden, rtol=orc.RTOL_TEST)
+        assert ok, ((m, n, k), ratio)
+        assert orc.max_rel_err(z.cpu().numpy(), orc.golden_fp64(x1, x2)) < 1e-5

@@ -14,6 +14,7 @@ def main():
     m, n, k = (int(v) for v in sys.argv[1:4])
     fields = {kv.split("=")[0]: int(kv.split("=")[1]) for kv in sys.argv[4:]}
     iters = fields.pop("iters", 200)
+    use_graph = fields.pop("graph", 0)   # graph=1: replay 20 back-to-back launches as one CUDA graph per iteration
     dev = "cuda:0"
     nbytes = 2 * (m * k + n * k + m * n)
     sets = max(2, int(2 * (126 << 20) / nbytes) + 2)
@@ -27,6 +28,21 @@ def main():
         else:
             dga.catlass_dynamic_matmul(a[i % sets], w[i % sets].t(), out=c[i % sets])
 
+    per = 1
+    if use_graph:
+        per = 20
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            for i in range(sets):
+                run(i)
+            side.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                for i in range(per):
+                    run(i)
+        inner = run
+        run = lambda i: g.replay()  # noqa: E731
+        iters = max(10, iters // per)
     for i in range(10):
         run(i)
     torch.cuda.synchronize()
@@ -36,9 +52,9 @@ def main():
         run(i)
     e1.record()
     torch.cuda.synchronize()
-    us = e0.elapsed_time(e1) * 1e3 / iters
-    print("%d %d %d %s dbg=%s: %.2f us  %.1f TFLOP/s  %.1f GB/s" % (
-        m, n, k, fields, os.environ.get("DGA_DEBUG_FLAGS", "0"), us, 2.0 * m * n * k / us / 1e6, nbytes / us / 1e3))
+    us = e0.elapsed_time(e1) * 1e3 / iters / per
+    print("%d %d %d %s dbg=%s pdl=%s: %.2f us  %.1f TFLOP/s  %.1f GB/s" % (
+        m, n, k, fields, os.environ.get("DGA_DEBUG_FLAGS", "0"), os.environ.get("DGA_PDL", "1"), us, 2.0 * m * n * k / us / 1e6, nbytes / us / 1e3))
 
 
 if __name__ == "__main__":
