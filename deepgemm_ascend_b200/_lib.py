@@ -80,6 +80,7 @@ SIGNATURES = {
                                             ctypes.c_int64, _P(_u64), _P(_vp)]),
     "dgaNShardMatmul": (_i32, [_vp, _u64, _vp, _vp]),
     "dgaSetOption": (_i32, [ctypes.c_char_p, ctypes.c_int64]),
+    "dgaDebugReadTrace": (_i32, [_P(_u64), _u32]),
     "dgaGetLastError": (ctypes.c_char_p, []),
     "dgaKernelLaunchCount": (_u64, []),
     "dgaVersion": (ctypes.c_char_p, []),

@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <cudaTypedefs.h>
 
+#include <algorithm>
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
@@ -27,6 +28,7 @@ static std::atomic<uint64_t> g_launches{0};
 // tuning knobs (dgaSetOption); -1 = built-in default
 static std::atomic<int64_t> g_opt_splitk_prefetch{-1};
 static std::atomic<int64_t> g_opt_pdl{-1};
+static std::atomic<int64_t> g_opt_splitk_batch{-1};
 
 #define DGA_CUDA(expr)                                                                       \
     do {                                                                                     \
@@ -110,6 +112,19 @@ struct DenseLaunch {
     void* peer_d[kMaxPeers] = {};
     PeerMaps peers{};
 };
+
+// DGA_DEBUG_FLAGS & 16: every CTA of the persistent kernel writes six timestamps (see GemmParams::trace); the last
+// launch's records are read back with dgaDebugReadTrace.  Developer aid for launch-ramp / tail / clock questions.
+constexpr uint32_t kTraceWords = 6 * 1024;
+static unsigned long long* trace_buffer() {
+    static unsigned long long* buf = [] {
+        void* p = nullptr;
+        if (cudaMalloc(&p, kTraceWords * 8) != cudaSuccess) return static_cast<unsigned long long*>(nullptr);
+        cudaMemset(p, 0, kTraceWords * 8);
+        return static_cast<unsigned long long*>(p);
+    }();
+    return buf;
+}
 
 // Launch attributes shared by every tensor-core kernel: the cluster shape and programmatic dependent launch (the
 // kernels call griddepcontrol.wait before their first global access, so the prologue of launch i+1 overlaps the
@@ -236,6 +251,7 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     }
     static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
     gp.debug = dbg;
+    if (dbg & 16) gp.trace = trace_buffer();
     if (cta == 2)
         return p.layoutTagB == 1 ? launch_common_out<2, false>(L, gp, stream) : launch_common_out<2, true>(L, gp, stream);
     return p.layoutTagB == 1 ? launch_common_out<1, false>(L, gp, stream) : launch_common_out<1, true>(L, gp, stream);
@@ -284,8 +300,13 @@ static int launch_splitk(DenseLaunch& L, cudaStream_t stream) {
     while (cols < m_pad) cols <<= 1;
     sp.tmem_cols = cols;
     const int64_t pf = g_opt_splitk_prefetch.load(std::memory_order_relaxed);
-    sp.prefetch_kb = pf >= 0 ? uint32_t(pf) : 8u;
+    sp.prefetch_kb = pf >= 0 ? uint32_t(pf) : 4u;
+    const int64_t ib = g_opt_splitk_batch.load(std::memory_order_relaxed);
+    sp.issue_batch = std::max<uint32_t>(1u, std::min<uint32_t>(ib > 0 ? uint32_t(ib) : 1u, p.stages));
     sp.out = L.eff.d;
+    static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
+    sp.trace = (dbg & 16) && L.plan.blockDim * 12 <= kTraceWords ? trace_buffer() : nullptr;
+    // the drained ring doubles as the fp32 staging tile [m][128] of the reduction
     if (sp.k_blocks < sp.split || uint64_t(p.stages) * (16384 + m_pad * 128) < uint64_t(m_pad) * 512) {
         set_error("split-K plan infeasible for this shape");
         return ACLNN_ERR_INNER_TILING_ERROR;
@@ -1121,10 +1142,18 @@ aclnnStatus dgaSetOption(const char* name, int64_t value) {
     if (name == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
     if (std::strcmp(name, "splitk_prefetch_kb") == 0) g_opt_splitk_prefetch.store(value);
     else if (std::strcmp(name, "pdl") == 0) g_opt_pdl.store(value);
+    else if (std::strcmp(name, "splitk_issue_batch") == 0) g_opt_splitk_batch.store(value);
     else {
         set_error(std::string("unknown option ") + name);
         return ACLNN_ERR_PARAM_INVALID;
     }
+    return ACLNN_SUCCESS;
+}
+aclnnStatus dgaDebugReadTrace(uint64_t* out, uint32_t words) {
+    if (out == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    unsigned long long* buf = trace_buffer();
+    if (buf == nullptr) return ACLNN_ERR_RUNTIME_ERROR;
+    DGA_CUDA(cudaMemcpy(out, buf, size_t(std::min(words, kTraceWords)) * 8, cudaMemcpyDeviceToHost));
     return ACLNN_SUCCESS;
 }
 const char* dgaGetLastError(void) { return last_error(); }

@@ -56,6 +56,7 @@ struct GemmParams {
     uint32_t dp_tiles, sk_tiles;
     uint32_t num_peers;      // extra destinations of every output chunk (PeerMaps)
     uint32_t epi_cols;       // columns per TMA store: 32, or 64 for 16-bit outputs when block_n % 64 == 0 (128-byte rows)
+    unsigned long long* trace; // debug & 16: per CTA {t_start, t_first_data, t_last_mma_issued, t_end (ns), clk_start, clk_end}
     float* sk_partials;      // [cluster][head/tail][cta rank][128][block_n] fp32
     int32_t* sk_sems;        // [sk tile][cta rank] arrival counters, zero on entry and on exit
 };
@@ -226,6 +227,11 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                   const GemmParams p) {
     static_assert(!(kMx && kBMn), "block-scaled fp8 wants K-major operands");
     ptx::grid_dep_launch();   // the next grid on the stream may set itself up while this one runs
+    const bool tracing = (p.debug & 16) != 0 && p.trace != nullptr;
+    if (tracing && threadIdx.x == 0) {
+        p.trace[blockIdx.x * 6 + 0] = ptx::globaltimer();
+        p.trace[blockIdx.x * 6 + 4] = clock64();
+    }
     if (p.gate != nullptr) {
         ptx::grid_dep_wait();     // the flag was written by the previous grid
         if (*p.gate != p.gate_expect) return;   // grid-uniform
@@ -377,6 +383,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                 for (uint32_t kb = kb0; kb < k_blocks; ++kb) {
                     ptx::mbar_wait(&full_bar[stage], phase);
                     ptx::tc_fence_after();
+                    if (tracing && iter == 0 && kb == kb0 && lane == 0) p.trace[blockIdx.x * 6 + 1] = ptx::globaltimer();
                     if (ptx::elect_one()) {
                         const uint32_t a_lo = a_lo0 + stage * a_step;
                         const uint32_t b_lo = b_lo0 + stage * b_step;
@@ -409,6 +416,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                     if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
             }
+            if (tracing && lane == 0) p.trace[blockIdx.x * 6 + 2] = ptx::globaltimer();
         }
     } else if (warp >= 4) {
         // ------------------------------------------------------- epilogue
@@ -549,6 +557,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     ptx::tc_fence_before();
     if constexpr (kCta == 2) ptx::cluster_sync(); else __syncthreads();
     if (warp == 2) ptx::tmem_dealloc<kCta>(tmem_base, 512);
+    if (tracing && threadIdx.x == 0) {
+        p.trace[blockIdx.x * 6 + 3] = ptx::globaltimer();
+        p.trace[blockIdx.x * 6 + 5] = clock64();
+    }
 }
 
 }  // namespace dga

@@ -4,9 +4,12 @@
 // Swap-AB: the 128 weight rows of a tile sit on the UMMA M axis (TMEM lanes),
 // the (padded) M activations on the UMMA N axis (TMEM columns), so no tensor
 // work is wasted on padding M up to 128.  K is split across the CTAs of a
-// thread-block cluster; their fp32 partials are reduced through distributed
-// shared memory in a fixed order (deterministic), so no workspace, no atomics
-// and no second kernel are needed.
+// thread-block cluster.  Each CTA owns a block of activation rows: every CTA
+// stages its fp32 partial tile in its own shared memory (over the drained ring)
+// and pushes each owner's rows there with one bulk DSMEM copy that completes on
+// the owner's mbarrier; the owner adds its `split` slots in a fixed order
+// (deterministic) and stores.  No workspace, no atomics, no second kernel, and
+// no cluster-wide barrier between the last MMA and the stores.
 // This is the B200 counterpart of what the reference reaches for with its
 // stream-K variant and (declared, never dispatched) multicore split-K kernel
 // type 3 (op_kernel/catlass_dynamic_matmul_tiling_key.h:117-130,
@@ -27,27 +30,29 @@ struct SmallMParams {
     uint32_t ldc;        // elements
     uint32_t idesc;
     uint32_t tmem_cols;  // power of two >= max(32, m_pad)
+    uint32_t issue_batch; // K blocks whose loads the producer issues back to back (<= num_stages)
+    unsigned long long* trace; // debug: per CTA 12 words (see tools/trace_smallm.py); nullptr = off
     uint32_t prefetch_kb; // K blocks of this CTA's weight slice pulled into L2 before the grid-dependency wait
     void* out;
 };
 
 struct SmallMSmem {
-    uint32_t w_bytes, x_bytes, stage_bytes, off_bar, total;
+    uint32_t w_bytes, x_bytes, stage_bytes, off_red, off_bar, total;
 };
-__host__ __device__ inline SmallMSmem make_smallm_smem(uint32_t m_pad, uint32_t stages) {
+// ring (reused as the staging tile [m][128] fp32 once drained) | reduction slots red[src CTA][owned row][128] fp32
+// (split > 1 only; written by the peers while this CTA may still be streaming, hence not aliased) | barriers
+__host__ __device__ inline uint32_t smallm_red_bytes(uint32_t m_pad, uint32_t split) {
+    return split > 1 ? split * ((m_pad + split - 1) / split) * 512u : 0u;
+}
+__host__ __device__ inline SmallMSmem make_smallm_smem(uint32_t m_pad, uint32_t stages, uint32_t split) {
     SmallMSmem l;
     l.w_bytes = 128 * 128;
     l.x_bytes = m_pad * 128;
     l.stage_bytes = l.w_bytes + l.x_bytes;
-    l.off_bar = stages * l.stage_bytes;
-    l.total = l.off_bar + (2 * stages + 2) * 8 + 16;
+    l.off_red = stages * l.stage_bytes;
+    l.off_bar = l.off_red + smallm_red_bytes(m_pad, split);
+    l.total = l.off_bar + (2 * stages + 4) * 8 + 16;
     return l;
-}
-
-__device__ __forceinline__ float ld_dsmem_f32(uint32_t cluster_addr) {
-    float v;
-    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(cluster_addr));
-    return v;
 }
 
 template <typename OutT>
@@ -65,6 +70,8 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
     ptx::grid_dep_launch();
+    unsigned long long* tr = p.trace != nullptr ? p.trace + blockIdx.x * 12 : nullptr;
+    if (tr != nullptr && threadIdx.x == 0) { tr[0] = ptx::globaltimer(); tr[2] = clock64(); }
 
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lane = threadIdx.x & 31;
@@ -77,11 +84,13 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     const uint32_t kb0 = static_cast<uint32_t>((static_cast<uint64_t>(rank) * p.k_blocks) / split);
     const uint32_t kb1 = static_cast<uint32_t>((static_cast<uint64_t>(rank + 1) * p.k_blocks) / split);
 
-    const SmallMSmem L = make_smallm_smem(p.m_pad, stages);
+    const SmallMSmem L = make_smallm_smem(p.m_pad, stages, split);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.off_bar);
     uint64_t* empty_bar = full_bar + stages;
     uint64_t* tmem_full_bar = empty_bar + stages;
-    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 2);
+    uint64_t* red_full_bar = tmem_full_bar + 1;   // completes when every peer's partial of this CTA's rows has landed
+    uint64_t* ack_bar = tmem_full_bar + 2;        // one arrival per owner that has received this CTA's partial
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 4);
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tensormap(&tm_w);
@@ -99,6 +108,9 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
             ptx::mbar_init(&empty_bar[s], 1);
         }
         ptx::mbar_init(tmem_full_bar, 1);
+        ptx::mbar_init(red_full_bar, 1);
+        // owners = CTAs that hold at least one activation row
+        ptx::mbar_init(ack_bar, min(split, (p.m + (p.m + split - 1) / split - 1) / ((p.m + split - 1) / split)));
         ptx::fence_mbar_init();
     }
     if (warp == 2) ptx::tmem_alloc<1>(tmem_ptr_smem, p.tmem_cols);
@@ -106,21 +118,37 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
+    // Peers will write into this CTA's reduction slots and signal its mbarrier: they may only do so once it is known
+    // to be running with the barrier initialised (fence_mbar_init above).  Arrive now, wait (phase 1 of the cluster
+    // barrier) just before the first remote access, a whole K slice later.
+    if (split > 1) ptx::cluster_arrive_relaxed();
+    if (tr != nullptr && threadIdx.x == 0) tr[3] = clock64();
     ptx::grid_dep_wait();   // the predecessor on the stream may still have been running up to here
+    if (tr != nullptr && threadIdx.x == 0) { tr[4] = clock64(); tr[11] = ptx::globaltimer(); }
 
     if (warp == 0) {
         if (lane == 0) {
+            // Loads go out `issue_batch` K blocks at a time: the 128-byte pieces of one weight row that belong to
+            // consecutive K blocks then reach the memory controller together (longer runs per DRAM page).
             uint32_t stage = 0, phase = 0;
-            for (uint32_t kb = kb0; kb < kb1; ++kb) {
-                ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-                uint8_t* sw = smem + stage * L.stage_bytes;
-                // W is read exactly once: do not let it push X out of L2
-                ptx::tma_load_2d(&tm_w, &full_bar[stage], sw, static_cast<int32_t>(kb * 64),
-                                 static_cast<int32_t>(n0), ptx::kEvictFirst);
-                ptx::tma_load_2d(&tm_x, &full_bar[stage], sw + L.w_bytes, static_cast<int32_t>(kb * 64), 0,
-                                 ptx::kEvictLast);
-                ptx::mbar_arrive_expect_tx(&full_bar[stage], L.stage_bytes);
-                if (++stage == stages) { stage = 0; phase ^= 1; }
+            const uint32_t batch = p.issue_batch;
+            for (uint32_t kb = kb0; kb < kb1;) {
+                const uint32_t nb = min(batch, kb1 - kb);
+                uint32_t s2 = stage, ph2 = phase;
+                for (uint32_t j = 0; j < nb; ++j) {
+                    ptx::mbar_wait(&empty_bar[s2], ph2 ^ 1);
+                    if (++s2 == stages) { s2 = 0; ph2 ^= 1; }
+                }
+                for (uint32_t j = 0; j < nb; ++j, ++kb) {
+                    uint8_t* sw = smem + stage * L.stage_bytes;
+                    // W is read exactly once: do not let it push X out of L2
+                    ptx::tma_load_2d(&tm_w, &full_bar[stage], sw, static_cast<int32_t>(kb * 64),
+                                     static_cast<int32_t>(n0), ptx::kEvictFirst);
+                    ptx::tma_load_2d(&tm_x, &full_bar[stage], sw + L.w_bytes, static_cast<int32_t>(kb * 64), 0,
+                                     ptx::kEvictLast);
+                    ptx::mbar_arrive_expect_tx(&full_bar[stage], L.stage_bytes);
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
             }
         }
         __syncwarp();
@@ -132,6 +160,7 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
             for (uint32_t kb = kb0; kb < kb1; ++kb) {
                 ptx::mbar_wait(&full_bar[stage], phase);
                 ptx::tc_fence_after();
+                if (tr != nullptr && kb == kb0) tr[5] = clock64();
                 const uint64_t w_desc = hi | (lo0 + stage * (L.stage_bytes >> 4));
                 const uint64_t x_desc = w_desc + (L.w_bytes >> 4);
 #pragma unroll
@@ -141,22 +170,32 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
                 if (kb + 1 == kb1) ptx::mma_commit<1>(tmem_full_bar);
                 if (++stage == stages) { stage = 0; phase ^= 1; }
             }
+            if (tr != nullptr) tr[6] = clock64();
         }
         __syncwarp();
     }
 
     OutT* out = reinterpret_cast<OutT*>(p.out);
-    // Partial tile -> registers.  After tmem_full fires every MMA (hence every
-    // smem read of the ring) has completed, so the ring is reused as the
-    // reduction buffer red[m][128] (fp32).
+    // Ownership of the activation rows inside a cluster: CTA d reduces rows [d * rows_per, (d + 1) * rows_per) ∩ [0, m)
+    const uint32_t rows_per = (p.m + split - 1) / split;
+    auto rows_of = [&](uint32_t d) { return d * rows_per >= p.m ? 0u : min(rows_per, p.m - d * rows_per); };
+    const uint32_t my_rows = rows_of(rank);
+    if (split > 1) {
+        ptx::cluster_wait();   // every CTA of the cluster is running (see cluster_arrive_relaxed above)
+        if (threadIdx.x == 0 && my_rows != 0) ptx::mbar_arrive_expect_tx(red_full_bar, split * my_rows * 512);
+    }
+    // Partial tile -> registers -> staging tile -> the owners' reduction slots (or straight to C when K is not split).
     if (warp >= 4) {
         const uint32_t row = threadIdx.x - 128;  // weight row inside the tile == TMEM lane
         const uint32_t lane_base = (warp & 3) * 32;
         ptx::mbar_wait(tmem_full_bar, 0);
         ptx::tc_fence_after();
+        if (tr != nullptr && threadIdx.x == 128) tr[7] = clock64();
         const uint32_t taddr = tmem_base + (lane_base << 16);
         const bool n_ok = n0 + row < p.n;
-        for (uint32_t c = 0; c < p.m_pad; c += 16) {
+        // tmem_full fired: every MMA, hence every read of the ring, has completed; the ring is the staging tile now
+        float* stage_out = reinterpret_cast<float*>(smem);
+        for (uint32_t c = 0; c < p.m; c += 16) {   // columns beyond m are padding: never read
             uint32_t v[16];
             ptx::tmem_ld_32x16(taddr + c, v);
             ptx::tmem_ld_wait();
@@ -166,44 +205,69 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
                     if (n_ok && c + j < p.m)
                         store_out<OutT>(out + static_cast<uint64_t>(c + j) * p.ldc + n0 + row, __uint_as_float(v[j]));
             } else {
-                float* red = reinterpret_cast<float*>(smem);
 #pragma unroll
-                for (uint32_t j = 0; j < 16; ++j) red[(c + j) * 128 + row] = __uint_as_float(v[j]);
+                for (uint32_t j = 0; j < 16; ++j)
+                    if (c + j < p.m) stage_out[(c + j) * 128 + row] = __uint_as_float(v[j]);
             }
         }
         ptx::tc_fence_before();
+        if (split > 1) {
+            ptx::fence_async_smem();          // generic-proxy writes -> visible to the bulk-copy engine
+            ptx::named_bar_sync(1, 128);
+            if (row < split) {
+                // thread d ships owner d's rows: stage_out[d * rows_per ...] -> red[rank][0 ...] of CTA d
+                const uint32_t cnt = rows_of(row);
+                if (cnt != 0)
+                    ptx::dsmem_bulk_copy(smem_base + L.off_red + rank * rows_per * 512,
+                                         smem_base + row * rows_per * 512, cnt * 512, red_full_bar, row);
+            }
+        }
     }
 
     if (split > 1) {
-        ptx::cluster_sync();  // all partials visible cluster-wide
-        // CTA `rank` finalises activations rank, rank + split, ...; 256 threads = 2 rows of 128 columns
-        const uint32_t col = threadIdx.x & 127;
-        const uint32_t half = threadIdx.x >> 7;
-        const uint32_t local = smem_base + col * 4;
-        const bool n_ok = n0 + col < p.n;
-        constexpr uint32_t kU = 4;
-        for (uint32_t mi = rank + split * half; mi < p.m; mi += split * 2 * kU) {
-            float acc[kU];
+        if (my_rows != 0) {
+            ptx::mbar_wait(red_full_bar, 0);
+            if (tr != nullptr && threadIdx.x == 0) tr[8] = clock64();
+            // tell every source that its staging tile has been read (it may leave); then reduce
+            if (threadIdx.x < split) ptx::mbar_arrive_remote(ack_bar, threadIdx.x);
+            // 8 rows x 32 four-column groups at a time; slots are added in CTA order (deterministic)
+            const uint32_t cg = (threadIdx.x & 31) * 4;
+            const float* red = reinterpret_cast<const float*>(smem + L.off_red);
+            const bool vec_ok = (reinterpret_cast<uintptr_t>(out) % (4 * sizeof(OutT)) == 0) &&
+                                (p.ldc % 4 == 0) && (n0 + 128 <= p.n);
+            for (uint32_t r = threadIdx.x >> 5; r < my_rows; r += 8) {
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (uint32_t s = 0; s < split; ++s) {
+                    const float4 v = *reinterpret_cast<const float4*>(red + (s * rows_per + r) * 128 + cg);
+                    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+                }
+                OutT* dst = out + static_cast<uint64_t>(rank * rows_per + r) * p.ldc + n0 + cg;
+                if (vec_ok) {
+                    if constexpr (sizeof(OutT) == 4) {
+                        *reinterpret_cast<float4*>(dst) = acc;
+                    } else {
+                        uint2 w;
+                        w.x = OutPack<OutT>::pack(acc.x, acc.y);
+                        w.y = OutPack<OutT>::pack(acc.z, acc.w);
+                        *reinterpret_cast<uint2*>(dst) = w;
+                    }
+                } else {
+                    const float a4[4] = {acc.x, acc.y, acc.z, acc.w};
 #pragma unroll
-            for (uint32_t u = 0; u < kU; ++u) acc[u] = 0.f;
-            for (uint32_t s = 0; s < split; ++s) {
-#pragma unroll
-                for (uint32_t u = 0; u < kU; ++u) {
-                    const uint32_t mm = mi + u * split * 2;
-                    if (mm < p.m) acc[u] += ld_dsmem_f32(ptx::mapa(local + mm * 512, s));
+                    for (uint32_t j = 0; j < 4; ++j)
+                        if (n0 + cg + j < p.n) store_out<OutT>(dst + j, a4[j]);
                 }
             }
-#pragma unroll
-            for (uint32_t u = 0; u < kU; ++u) {
-                const uint32_t mm = mi + u * split * 2;
-                if (mm < p.m && n_ok) store_out<OutT>(out + static_cast<uint64_t>(mm) * p.ldc + n0 + col, acc[u]);
-            }
         }
-        ptx::cluster_sync();  // nobody leaves while a peer still reads its smem
+        if (tr != nullptr && threadIdx.x == 0) tr[9] = clock64();
+        // A CTA's outgoing copies read its staging tile until the owners have seen them complete
+        ptx::mbar_wait(ack_bar, 0);
+        __syncthreads();
     } else {
         __syncthreads();
     }
     if (warp == 2) ptx::tmem_dealloc<1>(tmem_base, p.tmem_cols);
+    if (tr != nullptr && threadIdx.x == 0) { tr[10] = clock64(); tr[1] = ptx::globaltimer(); }
 }
 
 }  // namespace dga

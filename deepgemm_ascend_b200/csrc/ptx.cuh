@@ -46,6 +46,12 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+__device__ __forceinline__ unsigned long long globaltimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 // ------------------------------------------- programmatic dependent launch
 // Launched with cudaLaunchAttributeProgrammaticStreamSerialization, a grid may start while its predecessor on
 // the stream is still draining: everything up to grid_dep_wait() (barrier init, TMEM allocation, descriptor
@@ -57,6 +63,9 @@ __device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.w
 // ----------------------------------------------------------------- cluster
 __device__ __forceinline__ void cluster_arrive() {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_arrive_relaxed() {
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void cluster_wait() {
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -80,6 +89,20 @@ __device__ __forceinline__ float4 ld_cluster_f32x4(uint32_t cluster_addr) {
     asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
                  : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(cluster_addr) : "memory");
     return v;
+}
+
+// Bulk copy from this CTA's shared memory into the shared memory of CTA `cta` of the cluster (same offsets there),
+// completing (complete_tx) on that CTA's mbarrier `bar`.  16-byte granular.
+__device__ __forceinline__ void dsmem_bulk_copy(uint32_t dst_local_addr, uint32_t src_local_addr, uint32_t bytes,
+                                                uint64_t* bar, uint32_t cta) {
+    asm volatile(
+        "{\n\t"
+        ".reg .b32 rd, rb;\n\t"
+        "mapa.shared::cluster.u32 rd, %0, %4;\n\t"
+        "mapa.shared::cluster.u32 rb, %3, %4;\n\t"
+        "cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [rd], [%1], %2, [rb];\n\t"
+        "}\n"
+        :: "r"(dst_local_addr), "r"(src_local_addr), "r"(bytes), "r"(smem_u32(bar)), "r"(cta) : "memory");
 }
 
 // ---------------------------------------------------------------- mbarrier

@@ -40,9 +40,13 @@ uint32_t common_smem_bytes(uint32_t block_n, uint32_t cta_group, uint32_t stages
     return 2 * d_stage + stages * (a_stage + b_stage) + (2 * stages + 4) * 8 + 16 + 1024;
 }
 
-uint32_t splitk_smem_bytes(uint32_t m_pad, uint32_t stages) {
+// fp32 reduction slots of the split-K kernel: split x ceil(m_pad / split) rows of 128 floats (smallm_red_bytes)
+static uint32_t splitk_red_bytes(uint32_t m_pad, uint32_t split) {
+    return split > 1 ? split * ceil_div(m_pad, split) * 512u : 0u;
+}
+uint32_t splitk_smem_bytes(uint32_t m_pad, uint32_t stages, uint32_t split) {
     const uint32_t stage = 128 * 128 + m_pad * 128;
-    return stages * stage + (2 * stages + 2) * 8 + 16 + 1024;
+    return stages * stage + splitk_red_bytes(m_pad, split) + (2 * stages + 2) * 8 + 16 + 1024;
 }
 
 namespace {
@@ -118,23 +122,34 @@ SplitCand eval_splitk(const DgaTilingPlan& p, uint32_t split) {
     SplitCand c{split, 0, 0, 1e30};
     if (kb < split) return c;
     const uint32_t stage = 128 * 128 + m_pad * 128;
-    c.stages = max_stages(stage, 1024 + 256, hw.smemBytes, 12);
-    // the reduce buffer (m_pad x 128 fp32) reuses the ring
+    // Two CTAs share an SM when each stays under half of the shared memory.  Measured on B200 (N=4096, K=7168,
+    // profiles/r01_smallm_sweep.log): 256 CTAs at two per SM with a 3-4 stage ring stream faster than 128 CTAs with
+    // the deepest ring (M=16: 11.6 vs 13.4 us), so that is preferred whenever a ring of >= 3 stages still fits.
+    const uint32_t fixed = 1024 + 256 + splitk_red_bytes(m_pad, split);
+    uint32_t per_sm = 2;
+    c.stages = max_stages(stage, fixed, hw.smemBytes / 2 - 1024, 4);
+    if (c.stages < 3) {
+        per_sm = 1;
+        c.stages = max_stages(stage, fixed, hw.smemBytes, 12);
+    }
+    // the drained ring doubles as the fp32 staging tile [m][128] of the reduction
     if (c.stages < 2 || c.stages * stage < m_pad * 512) return c;
     const uint32_t tiles = ceil_div(p.n, 128);
     c.grid = tiles * split;
     // clusters larger than 2 cannot use every SM (GPC granularity)
-    const uint32_t usable = split <= 2 ? hw.smCount : split == 4 ? 132 : 128;
+    const uint32_t usable = (split <= 2 ? hw.smCount : split == 4 ? 132 : 128) * per_sm;
     const double waves = std::ceil(double(c.grid) / usable);
     const double kb_per = std::ceil(double(kb) / split);
     const double cta_bytes = kb_per * stage;
     const uint32_t active = std::min(c.grid, usable);
-    // each SM streams at most ~1/100 of HBM bandwidth; all active SMs share HBM
-    const double per_sm_gbs = std::min(hw.hbmGBs / active, hw.hbmGBs / 100.0);
-    const double stream_us = waves * cta_bytes / (per_sm_gbs * 1e3);
+    // each CTA streams at most ~1/100 of HBM bandwidth; all active CTAs share HBM
+    const double per_cta_gbs = std::min(hw.hbmGBs / active, hw.hbmGBs / 100.0);
+    const double stream_us = waves * cta_bytes / (per_cta_gbs * 1e3);
     const double mma_us = waves * kb_per * 4 * std::max(m_pad, 32u) / 2.0 / (kClockGHz * 1e3);
-    const double reduce_us = split > 1 ? 1.5 + m_pad * 0.01 * split : 0.5;
-    c.us = std::max(stream_us, mma_us) + reduce_us + kLaunchUs;
+    // tail: partial tile -> staging -> bulk DSMEM copies -> owner's sum and store (measured 1.3 us at M=16, 2.8 at M=64)
+    const double reduce_us = split > 1 ? 1.0 + m_pad * 0.03 : 0.5;
+    // every wave pays its own start-up and reduction tail
+    c.us = std::max(stream_us, mma_us) + waves * (reduce_us + 1.5) + kLaunchUs;
     return c;
 }
 
@@ -189,13 +204,19 @@ int finalize_plan(DgaTilingPlan& p) {
             return ACLNN_ERR_INNER_TILING_ERROR;
         }
         if (p.splitkFactor == 0) p.splitkFactor = 1;
-        if (p.stages == 0) p.stages = static_cast<uint8_t>(max_stages(128 * 128 + m_pad * 128, 1280, hw.smemBytes, 12));
+        const uint32_t fixed = 1280 + splitk_red_bytes(m_pad, p.splitkFactor);
+        const uint32_t cap = max_stages(128 * 128 + m_pad * 128, fixed, hw.smemBytes, 12);
+        if (p.stages == 0 || p.stages > cap) p.stages = static_cast<uint8_t>(cap);
+        if (p.stages < 2 || p.stages * (128 * 128 + m_pad * 128) < m_pad * 512) {
+            set_error("split-K plan does not fit shared memory");
+            return ACLNN_ERR_INNER_TILING_ERROR;
+        }
         p.m1 = static_cast<uint16_t>(m_pad);
         p.n1 = 128;
         p.k1 = 64;
         p.ctaGroup = 1;
         p.blockDim = ceil_div(p.n, 128) * p.splitkFactor;
-        p.smemBytes = splitk_smem_bytes(m_pad, p.stages);
+        p.smemBytes = splitk_smem_bytes(m_pad, p.stages, p.splitkFactor);
         p.workspaceBytes = 0;
         p.paddingTagC = 0;   // this kernel stores C with plain st.global: any pitch will do
     } else {
@@ -286,16 +307,18 @@ int select_kernel(DgaTilingPlan& p) {
     // --- small-M swap-AB split-K candidates
     SplitCand sbest{0, 0, 0, 1e30};
     if (p.m <= 256 && p.layoutTagB == 1 && in_b == 2) {
-        for (uint32_t s : {1u, 2u, 4u, 8u}) {
+        // ties go to the larger split: more CTAs in flight hide each other's start-up and reduction tails
+        for (uint32_t s : {8u, 4u, 2u, 1u}) {
             SplitCand c = eval_splitk(p, s);
             if (c.us < sbest.us) sbest = c;
         }
     }
     // M <= 64 is HBM-bound by the weight: a 256-row pair tile would waste >= 3/4 of the tensor work and, worse,
     // most of the SMs' load slots, so the streaming kernel always wins there; above that the estimates decide.
-    // measured on B200 (N=4096, K=7168): the swap-AB kernel also wins at M = 128 (20.6 vs 28.9 us) and M = 256
-    // (24.7 vs 29.0 us); the estimates are too coarse there, so the rule is explicit.
-    if (sbest.split != 0 && (sbest.us < best.us || p.m <= 256)) {
+    // measured on B200 (N=4096, K=7168): the swap-AB kernel also wins at M = 128 (17.7 vs 28.9 us); the estimates
+    // are too coarse there, so the rule is explicit.  Beyond 128 rows the fp32 reduction slots (m x 512 B per CTA)
+    // crowd out the ring and the estimates decide.
+    if (sbest.split != 0 && (sbest.us < best.us || p.m <= 128)) {
         p.kernelSerial = DGA_KERNEL_SPLITK;
         p.splitkFactor = static_cast<uint16_t>(sbest.split);
         p.stages = static_cast<uint8_t>(sbest.stages);

@@ -36,7 +36,7 @@ inline uint32_t epi_cols_host(uint32_t block_n, uint32_t out_bytes) { return (ou
 uint32_t common_smem_bytes(uint32_t block_n, uint32_t cta_group, uint32_t stages, uint32_t out_bytes,
                            uint32_t in_bytes);
 // Smem bytes of the swap-AB split-K kernel (gemm_smallm_sm100.cuh).
-uint32_t splitk_smem_bytes(uint32_t m_pad, uint32_t stages);
+uint32_t splitk_smem_bytes(uint32_t m_pad, uint32_t stages, uint32_t split);
 
 // Fills every field of `plan` from (m, n, k, dtype, outDtype, layoutTagB). Returns ACLNN_SUCCESS or an error.
 int select_kernel(DgaTilingPlan& plan);
