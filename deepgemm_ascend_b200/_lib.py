@@ -8,7 +8,7 @@ import os
 
 from . import build as _build
 
-ACL_FLOAT, ACL_FLOAT16, ACL_BF16, ACL_FLOAT8_E4M3FN = 0, 1, 27, 36
+ACL_FLOAT, ACL_FLOAT16, ACL_INT32, ACL_BF16, ACL_FLOAT8_E4M3FN = 0, 1, 3, 27, 36
 ACL_FORMAT_ND = 2
 ACLNN_SUCCESS = 0
 
@@ -79,6 +79,8 @@ SIGNATURES = {
     "dgaNShardMatmulGetWorkspaceSize": (_i32, [_P(AclTensor), _P(AclTensor), _P(_vp), _u32, _u32, ctypes.c_int64,
                                             ctypes.c_int64, _P(_u64), _P(_vp)]),
     "dgaNShardMatmul": (_i32, [_vp, _u64, _vp, _vp]),
+    "dgaMGroupedMatmulGetWorkspaceSize": (_i32, [_P(AclTensor)] * 4 + [_P(_u64), _P(_vp)]),
+    "dgaMGroupedMatmul": (_i32, [_vp, _u64, _vp, _vp]),
     "dgaSetOption": (_i32, [ctypes.c_char_p, ctypes.c_int64]),
     "dgaDebugReadTrace": (_i32, [_P(_u64), _u32]),
     "dgaGetLastError": (ctypes.c_char_p, []),

@@ -91,6 +91,33 @@ static int make_tmap_2d(CUtensorMap* map, const void* ptr, int32_t dtype, uint64
     return ACLNN_SUCCESS;
 }
 
+// 3-D row-major tensor [outer2, outer, inner]: pitch `ld` between rows, `ld2` between slabs (elements); box depth 1.
+static int make_tmap_3d(CUtensorMap* map, const void* ptr, int32_t dtype, uint64_t inner, uint64_t outer, uint64_t outer2,
+                        uint64_t ld, uint64_t ld2, uint32_t box_inner, uint32_t box_outer, CUtensorMapSwizzle swizzle) {
+    auto fn = encode_fn();
+    if (fn == nullptr) {
+        set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver)");
+        return ACLNN_ERR_RUNTIME_ERROR;
+    }
+    const uint32_t eb = elem_bytes(dtype);
+    cuuint64_t dims[3] = {inner, outer, outer2};
+    cuuint64_t strides[2] = {ld * eb, ld2 * eb};
+    cuuint32_t box[3] = {box_inner, box_outer, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || (strides[0] & 15) != 0 || (strides[1] & 15) != 0) {
+        set_error("TMA needs 16-byte aligned base pointers and pitches");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    CUresult r = fn(map, tmap_dtype(dtype), 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (3-D) failed with CUresult " + std::to_string(int(r)));
+        return ACLNN_ERR_RUNTIME_ERROR;
+    }
+    return ACLNN_SUCCESS;
+}
+
 // ---- launch records ---------------------------------------------------------------------------------
 struct DenseLaunch {
     DgaTilingPlan plan;
@@ -107,6 +134,12 @@ struct DenseLaunch {
     CUtensorMap tm_a, tm_b, tm_d;
     bool encoded = false;
     bool maps_fresh() const { return encoded && std::memcmp(&eff, &enc, sizeof(Operands)) == 0; }
+    // kModeBatched: `batch` independent GEMMs of one shape, slabs `slab_*` elements apart.
+    // kModeMGrouped: plan.m = M_total rows in 128-row blocks, weight [groups, N, K], group_index[M_total] on the device.
+    int mode = kModePlain;
+    uint32_t batch = 1, groups = 0;
+    uint64_t slab_a = 0, slab_b = 0, slab_d = 0;
+    const int32_t* group_index = nullptr;
     // N-sharded execution: the column slice of every peer's C (device pointers mapped into this process)
     uint32_t num_peers = 0;
     void* peer_d[kMaxPeers] = {};
@@ -155,9 +188,9 @@ static int set_smem_attr(K kernel, uint32_t bytes) {
     return ACLNN_SUCCESS;
 }
 
-template <int kCta, typename OutT, bool kBMn>
+template <int kCta, typename OutT, bool kBMn, int kMode = kModePlain>
 static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaStream_t stream) {
-    auto kernel = gemm_sm100_kernel<kCta, OutT, kBMn>;
+    auto kernel = gemm_sm100_kernel<kCta, OutT, kBMn, false, kMode>;
     int rc = set_smem_attr(kernel, L.plan.smemBytes);
     if (rc != ACLNN_SUCCESS) return rc;
     cudaLaunchConfig_t cfg{};
@@ -186,6 +219,29 @@ static int launch_common_out(const DenseLaunch& L, const GemmParams& gp, cudaStr
 static int encode_common(DenseLaunch& L) {
     const DgaTilingPlan& p = L.plan;
     const uint32_t cta = p.ctaGroup, load_n = p.n1 / cta;
+    if (L.mode != kModePlain) {
+        const uint32_t epi3 = epi_cols_for(p.n1, elem_bytes(p.outDtype));
+        const CUtensorMapSwizzle d_swz3 = epi3 * elem_bytes(p.outDtype) == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                                                                : CU_TENSOR_MAP_SWIZZLE_64B;
+        int rc3;
+        if (L.mode == kModeBatched) {
+            rc3 = make_tmap_3d(&L.tm_a, L.eff.a, p.dtype, p.k, p.m, L.batch, L.eff.lda, L.slab_a, 64, 128,
+                               CU_TENSOR_MAP_SWIZZLE_128B);
+            if (rc3 != ACLNN_SUCCESS) return rc3;
+            rc3 = make_tmap_3d(&L.tm_d, L.eff.d, p.outDtype, p.n, p.m, L.batch, L.eff.ldd, L.slab_d, epi3, 128, d_swz3);
+        } else {
+            rc3 = make_tmap_2d(&L.tm_a, L.eff.a, p.dtype, p.k, p.m, L.eff.lda, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+            if (rc3 != ACLNN_SUCCESS) return rc3;
+            rc3 = make_tmap_2d(&L.tm_d, L.eff.d, p.outDtype, p.n, p.m, L.eff.ldd, epi3, 128, d_swz3);
+        }
+        if (rc3 != ACLNN_SUCCESS) return rc3;
+        const uint64_t slabs = L.mode == kModeBatched ? L.batch : L.groups;
+        if (p.layoutTagB == 1)
+            return make_tmap_3d(&L.tm_b, L.eff.b, p.dtype, p.k, p.n, slabs, L.eff.ldb, L.slab_b, 64, load_n,
+                                CU_TENSOR_MAP_SWIZZLE_128B);
+        return make_tmap_3d(&L.tm_b, L.eff.b, p.dtype, p.n, p.k, slabs, L.eff.ldb, L.slab_b, 64, 64,
+                            CU_TENSOR_MAP_SWIZZLE_128B);
+    }
     int rc = make_tmap_2d(&L.tm_a, L.eff.a, p.dtype, p.k, p.m, L.eff.lda, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != ACLNN_SUCCESS) return rc;
     if (p.layoutTagB == 1)  // weight stored [N, K]
@@ -252,6 +308,25 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
     gp.debug = dbg;
     if (dbg & 16) gp.trace = trace_buffer();
+    if (L.mode != kModePlain) {
+        // single-CTA tiles only; the instances the two callers need: the framework's batched fp32-output GEMM over
+        // row-major B, and the MoE grouped GEMM over [G,N,K] weights with a 16-bit output
+        gp.tiles_per_batch = gp.dp_tiles;
+        gp.group_index = L.group_index;
+        if (L.mode == kModeBatched) gp.dp_tiles *= L.batch;
+        if (cta != 1 || p.kernelSerial == DGA_KERNEL_STREAMK) {
+            set_error("batched / grouped launches use single-CTA whole tiles");
+            return ACLNN_ERR_INNER_TILING_ERROR;
+        }
+        if (L.mode == kModeBatched && p.layoutTagB == 0 && p.outDtype == ACL_FLOAT)
+            return launch_common_inst<1, float, true, kModeBatched>(L, gp, stream);
+        if (L.mode == kModeMGrouped && p.layoutTagB == 1 && p.outDtype == ACL_BF16)
+            return launch_common_inst<1, __nv_bfloat16, false, kModeMGrouped>(L, gp, stream);
+        if (L.mode == kModeMGrouped && p.layoutTagB == 1 && p.outDtype == ACL_FLOAT16)
+            return launch_common_inst<1, __half, false, kModeMGrouped>(L, gp, stream);
+        set_error("this dtype / layout combination is not built for batched / grouped launches");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
     if (cta == 2)
         return p.layoutTagB == 1 ? launch_common_out<2, false>(L, gp, stream) : launch_common_out<2, true>(L, gp, stream);
     return p.layoutTagB == 1 ? launch_common_out<1, false>(L, gp, stream) : launch_common_out<1, true>(L, gp, stream);
@@ -966,6 +1041,83 @@ aclnnStatus dgaFp8BlockScaledMatmul(void* workspace, uint64_t workspaceSize, acl
     return rc;
 }
 
+// ---- M-grouped contiguous matmul (MoE) -------------------------------------------------------------------------
+static void seed_plan(DgaTilingPlan& p, uint32_t m, uint32_t n, uint32_t k, int32_t dtype, int32_t outDtype,
+                      int32_t layoutTagB);
+static int plan_single_cta(DgaTilingPlan& p, uint32_t slabs_of_tiles);
+aclnnStatus dgaMGroupedMatmulGetWorkspaceSize(const aclTensor* self, const aclTensor* weight, const aclTensor* groupIndex,
+                                              const aclTensor* out, uint64_t* workspaceSize, aclOpExecutor** executor) {
+    if (!self || !weight || !groupIndex || !out || !workspaceSize || !executor) {
+        set_error("null argument");
+        return ACLNN_ERR_PARAM_NULLPTR;
+    }
+    if (self->ndim != 2 || weight->ndim != 3 || groupIndex->ndim != 1 || out->ndim != 2) {
+        set_error("Invalid input dimensions. self [M,K], weight [G,N,K], groupIndex [M], out [M,N]");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (self->dtype != weight->dtype || !dtype_ok_in(self->dtype) || out->dtype != self->dtype ||
+        groupIndex->dtype != kAclInt32) {
+        set_error("self, weight and out must share a dtype in {float16, bfloat16}; groupIndex must be int32");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    const int64_t m = self->shape[0], k = self->shape[1], g = weight->shape[0], n = weight->shape[1];
+    if (weight->shape[2] != k) {
+        set_error("K dimension mismatch: self[1]=" + std::to_string(k) + " weight[2]=" + std::to_string(weight->shape[2]));
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (out->shape[0] != m || out->shape[1] != n || groupIndex->shape[0] != m) {
+        set_error("out must be [M, N] and groupIndex [M]");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (m <= 0 || n <= 0 || k <= 0 || g <= 0 || m > UINT32_MAX || n > UINT32_MAX || k > UINT32_MAX || m % 128 != 0) {
+        set_error("m, n, k, groups must be positive and M_total a multiple of 128 (every 128-row block has one group)");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (self->stride[1] != 1 || weight->stride[2] != 1 || out->stride[1] != 1 || groupIndex->stride[0] != 1 ||
+        self->stride[0] < k || weight->stride[1] < k || out->stride[0] < n ||
+        (g > 1 && weight->stride[0] < weight->stride[1] * n)) {
+        set_error("self, weight (K contiguous) and out must be row-major");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    aclOpExecutor* ex = new aclOpExecutor{};
+    DenseLaunch& L = ex->dense;
+    seed_plan(L.plan, uint32_t(m), uint32_t(n), uint32_t(k), self->dtype, out->dtype, /*layoutTagB=*/1);
+    L.a = self->data; L.b = weight->data; L.d = out->data;
+    L.lda = uint64_t(self->stride[0]); L.ldb = uint64_t(weight->stride[1]); L.ldd = uint64_t(out->stride[0]);
+    L.plan.strideA = L.lda; L.plan.strideB = L.ldb; L.plan.strideC = L.ldd;
+    L.mode = kModeMGrouped;
+    L.groups = uint32_t(g);
+    L.slab_b = g > 1 ? uint64_t(weight->stride[0]) : uint64_t(n) * L.ldb;
+    L.group_index = static_cast<const int32_t*>(groupIndex->data);
+    int rc = plan_single_cta(L.plan, 1);
+    const uint32_t eb = 2;
+    if (rc == ACLNN_SUCCESS &&
+        (((L.lda | L.ldb | L.ldd | L.slab_b) * eb) % 16 != 0 ||
+         ((reinterpret_cast<uintptr_t>(L.a) | reinterpret_cast<uintptr_t>(L.b) | reinterpret_cast<uintptr_t>(L.d)) & 15))) {
+        set_error("grouped matmul wants 16-byte aligned base pointers and pitches");
+        rc = ACLNN_ERR_INNER_TILING_ERROR;
+    }
+    if (rc != ACLNN_SUCCESS) {
+        delete ex;
+        return rc;
+    }
+    *workspaceSize = 0;
+    *executor = ex;
+    return ACLNN_SUCCESS;
+}
+aclnnStatus dgaMGroupedMatmul(void* workspace, uint64_t workspaceSize, aclOpExecutor* executor, aclrtStream stream) {
+    (void)workspace; (void)workspaceSize;
+    if (executor == nullptr || executor->is_fp8 || executor->dense.mode != kModeMGrouped) {
+        set_error("not a grouped-matmul executor");
+        return ACLNN_ERR_PARAM_NULLPTR;
+    }
+    DenseLaunch& L = executor->dense;
+    L.eff = {L.a, L.b, L.d, L.lda, L.ldb, L.ldd};
+    aclnnStatus rc = launch_common(L, static_cast<cudaStream_t>(stream), nullptr);
+    if (!executor->repeatable) delete executor;
+    return rc;
+}
+
 // ---- host tiling -------------------------------------------------------------------------------------
 static void seed_plan(DgaTilingPlan& p, uint32_t m, uint32_t n, uint32_t k, int32_t dtype, int32_t outDtype,
                       int32_t layoutTagB) {
@@ -1051,10 +1203,60 @@ static aclnnStatus framework_gemm(const void* x, const void* y, void* z, uint32_
     return rc;
 }
 
+// Single-CTA tile of a batched / grouped launch: widest N tile whose wave count over all SMs is minimal.
+static int plan_single_cta(DgaTilingPlan& p, uint32_t slabs_of_tiles) {
+    const uint32_t step = p.layoutTagB == 0 ? 64 : 32;
+    uint32_t best_n1 = 0;
+    uint64_t best_cost = ~0ull;
+    for (uint32_t n1 = 256; n1 >= 64; n1 -= step) {
+        const uint64_t tiles = uint64_t(ceil_div(p.m, 128)) * ceil_div(p.n, n1) * slabs_of_tiles;
+        const uint64_t waves = (tiles + platform().smCount - 1) / platform().smCount;
+        const uint64_t cost = waves * (n1 + 24);   // + per-tile overhead in column units
+        if (cost < best_cost) { best_cost = cost; best_n1 = n1; }
+    }
+    p.kernelSerial = DGA_KERNEL_COMMON;
+    p.ctaGroup = 1;
+    p.n1 = uint16_t(best_n1);
+    p.stages = 0;
+    p.splitkFactor = 1;
+    p.paddingTagA = p.paddingTagB = p.paddingTagC = 0;
+    int rc = finalize_plan(p);
+    if (rc != ACLNN_SUCCESS) return rc;
+    const uint64_t tiles = uint64_t(ceil_div(p.m, 128)) * ceil_div(p.n, p.n1) * slabs_of_tiles;
+    p.blockDim = uint32_t(std::min<uint64_t>(tiles, platform().smCount));
+    return ACLNN_SUCCESS;
+}
+
+// The framework kernel's batch loop (generate_code.hpp:149-153) as ONE launch: z[b] = x[b] * y[b], bf16 -> fp32,
+// row-major, 16-byte aligned pitches (k % 8 == 0, n % 8 == 0).
+static aclnnStatus framework_gemm_batched(const void* x, const void* y, void* z, uint32_t batch, uint32_t m, uint32_t n,
+                                          uint32_t k, cudaStream_t stream) {
+    DenseLaunch L;
+    seed_plan(L.plan, m, n, k, ACL_BF16, ACL_FLOAT, /*layoutTagB=*/0);
+    L.plan.strideA = k; L.plan.strideB = n; L.plan.strideC = n;
+    int rc = plan_single_cta(L.plan, batch);
+    if (rc != ACLNN_SUCCESS) return rc;
+    L.mode = kModeBatched;
+    L.batch = batch;
+    L.a = x; L.b = y; L.d = z;
+    L.lda = k; L.ldb = n; L.ldd = n;
+    L.slab_a = uint64_t(m) * k; L.slab_b = uint64_t(k) * n; L.slab_d = uint64_t(m) * n;
+    L.eff = {L.a, L.b, L.d, L.lda, L.ldb, L.ldd};
+    return launch_common(L, stream, nullptr);
+}
+
 aclnnStatus dgaRunMmadRtc(const void* x, const void* y, void* z, uint32_t batch, uint32_t m, uint32_t n, uint32_t k,
                           aclrtStream stream) {
     if (x == nullptr || y == nullptr || z == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bool aligned = k % 8 == 0 && n % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 &&
+                         (reinterpret_cast<uintptr_t>(y) & 15) == 0 && (reinterpret_cast<uintptr_t>(z) & 15) == 0;
+    if (batch > 1 && aligned) {
+        aclnnStatus rc = framework_gemm_batched(x, y, z, batch, m, n, k, s);
+        if (rc != ACLNN_SUCCESS) return rc;
+        DGA_CUDA(cudaStreamSynchronize(s));  // the reference blocks here (gemm.hpp:110)
+        return ACLNN_SUCCESS;
+    }
     for (uint32_t b = 0; b < batch; ++b) {  // batch loop of the reference kernel: generate_code.hpp:149-153
         const char* xb = static_cast<const char*>(x) + uint64_t(b) * m * k * 2;
         const char* yb = static_cast<const char*>(y) + uint64_t(b) * k * n * 2;

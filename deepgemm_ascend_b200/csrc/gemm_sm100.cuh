@@ -57,6 +57,10 @@ struct GemmParams {
     uint32_t num_peers;      // extra destinations of every output chunk (PeerMaps)
     uint32_t epi_cols;       // columns per TMA store: 32, or 64 for 16-bit outputs when block_n % 64 == 0 (128-byte rows)
     unsigned long long* trace; // debug & 16: per CTA {t_start, t_first_data, t_last_mma_issued, t_end (ns), clk_start, clk_end}
+    // kMode 1 (batched: A [B,M,K], B [B,K,N] or [B,N,K], D [B,M,N], 3-D tensor maps): tiles per batch entry
+    // kMode 2 (M-grouped contiguous: A [M_total,K], B [G,N,K], D [M_total,N]): group of every row, -1 = skip
+    uint32_t tiles_per_batch;
+    const int32_t* group_index;
     float* sk_partials;      // [cluster][head/tail][cta rank][128][block_n] fp32
     int32_t* sk_sems;        // [sk tile][cta rank] arrival counters, zero on entry and on exit
 };
@@ -219,13 +223,19 @@ __host__ __device__ inline SmemLayout make_smem_layout(uint32_t d_stage_bytes, u
 // scale words arrive pre-packed (4 consecutive 128-wide K blocks per 32-bit word, already in the 32x128-bit
 // order tcgen05.cp wants) from the workspace, one TMA box per 4 K blocks, and live in TMEM behind the two
 // accumulator stages.
-template <int kCta, typename OutT, bool kBMn, bool kMx = false>
+// kMode: 0 one GEMM; 1 batched (the framework kernel's batch loop, generate_code.hpp:149-153, as one launch: the
+// tile index carries the batch entry, 3-D tensor maps clip ragged M/N per entry); 2 M-grouped contiguous (MoE:
+// every 128-row block of A multiplies the weight of its group; rows of one block share a group, -1 skips it).
+// Modes 1 and 2 run single-CTA tiles (a CTA pair would have to share one B tile across two row blocks).
+constexpr int kModePlain = 0, kModeBatched = 1, kModeMGrouped = 2;
+template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                   const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_sfa,
                   const __grid_constant__ CUtensorMap tm_sfb, const __grid_constant__ PeerMaps peers,
                   const GemmParams p) {
     static_assert(!(kMx && kBMn), "block-scaled fp8 wants K-major operands");
+    static_assert(kMode == kModePlain || (kCta == 1 && !kMx), "batched / grouped modes are single-CTA, 16-bit");
     ptx::grid_dep_launch();   // the next grid on the stream may set itself up while this one runs
     const bool tracing = (p.debug & 16) != 0 && p.trace != nullptr;
     if (tracing && threadIdx.x == 0) {
@@ -296,9 +306,19 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         WorkItem w;
         while (it.next(w)) {
             uint32_t mb, nb;
-            tile_coords(p, w.tile, mb, nb);
+            int32_t z = 0;   // third tensor-map coordinate: batch entry (mode 1) or group (mode 2)
+            if constexpr (kMode == kModeBatched) {
+                z = static_cast<int32_t>(w.tile / p.tiles_per_batch);
+                tile_coords(p, w.tile - z * p.tiles_per_batch, mb, nb);
+            } else {
+                tile_coords(p, w.tile, mb, nb);
+            }
             const int32_t m_idx = static_cast<int32_t>(mb * (kBlockM * kCta) + cta_rank * kBlockM);
             const int32_t n_idx = static_cast<int32_t>(nb * p.block_n + cta_rank * load_n);
+            if constexpr (kMode == kModeMGrouped) {
+                z = __ldg(p.group_index + m_idx);
+                if (z < 0) continue;   // every role skips the same blocks
+            }
             for (uint32_t kb = w.kb0; kb < w.kb1; ++kb) {
                 ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                 if (p.debug & 1) {
@@ -340,12 +360,18 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                         if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * (L.a_stage_bytes + L.b_stage_bytes + sf_bytes));
                         else ptx::mbar_arrive_remote(&full_bar[stage], 0);
                     } else {
-                        ptx::tma_load_2d(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
+                        if constexpr (kMode == kModeBatched) ptx::tma_load_3d(&tm_a, &full_bar[stage], sa, k_idx, m_idx, z);
+                        else ptx::tma_load_2d(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
                         if constexpr (kBMn) {
-                            for (uint32_t j = 0; j < load_n / 64; ++j)
-                                ptx::tma_load_2d(&tm_b, &full_bar[stage], sb + j * 8192, n_idx + j * 64, k_idx);
+                            for (uint32_t j = 0; j < load_n / 64; ++j) {
+                                if constexpr (kMode == kModePlain)
+                                    ptx::tma_load_2d(&tm_b, &full_bar[stage], sb + j * 8192, n_idx + j * 64, k_idx);
+                                else
+                                    ptx::tma_load_3d(&tm_b, &full_bar[stage], sb + j * 8192, n_idx + j * 64, k_idx, z);
+                            }
                         } else {
-                            ptx::tma_load_2d(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
+                            if constexpr (kMode == kModePlain) ptx::tma_load_2d(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
+                            else ptx::tma_load_3d(&tm_b, &full_bar[stage], sb, k_idx, n_idx, z);
                         }
                         ptx::mbar_arrive_expect_tx(&full_bar[stage], L.a_stage_bytes + L.b_stage_bytes + sf_bytes);
                     }
@@ -375,6 +401,11 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
             WorkIter it(p, cluster_id, num_clusters);
             WorkItem w;
             for (; it.next(w); ++iter) {
+                if constexpr (kMode == kModeMGrouped) {
+                    uint32_t mb, nb;
+                    tile_coords(p, w.tile, mb, nb);
+                    if (__ldg(p.group_index + mb * kBlockM) < 0) { --iter; continue; }
+                }
                 const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
                 ptx::mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
                 ptx::tc_fence_after();
@@ -426,6 +457,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         volatile uint32_t* sk_bcast = tmem_ptr_smem + 1;       // arrival count broadcast inside the epilogue warps
         // one 32-column chunk of this CTA's rows: registers -> staging smem -> TMA store
         const bool wide = p.epi_cols == 64;
+        int32_t zb = 0;   // batch entry of the tile being stored (mode 1)
         auto store_chunk = [&](const uint32_t (&v)[32], uint32_t m0, uint32_t col, uint32_t c, bool last) {
             const uint32_t half = wide ? (c & 1u) : 0u;
             if (half == 0) {
@@ -441,7 +473,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
             if (epi_tid == 0) {
                 const int32_t c0 = static_cast<int32_t>(col - half * kEpiCols);
                 if (m0 < p.m && !(p.debug & 4)) {
-                    ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes, c0, static_cast<int32_t>(m0));
+                    if constexpr (kMode == kModeBatched)
+                        ptx::tma_store_3d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes, c0, static_cast<int32_t>(m0), zb);
+                    else
+                        ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes, c0, static_cast<int32_t>(m0));
                     for (uint32_t i = 0; i < p.num_peers; ++i)   // same chunk into every peer's C (NVLink)
                         ptx::tma_store_2d(&peers.m[i], smem + L.off_d + buf * L.d_stage_bytes, c0,
                                           static_cast<int32_t>(m0));
@@ -454,9 +489,17 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         WorkItem w;
         for (; it.next(w); ++iter) {
             uint32_t mb, nb;
-            tile_coords(p, w.tile, mb, nb);
+            if constexpr (kMode == kModeBatched) {
+                zb = static_cast<int32_t>(w.tile / p.tiles_per_batch);
+                tile_coords(p, w.tile - zb * p.tiles_per_batch, mb, nb);
+            } else {
+                tile_coords(p, w.tile, mb, nb);
+            }
             const uint32_t m0 = mb * (kBlockM * kCta) + cta_rank * kBlockM;
             const uint32_t n0 = nb * p.block_n;
+            if constexpr (kMode == kModeMGrouped) {
+                if (__ldg(p.group_index + m0) < 0) { --iter; continue; }
+            }
             const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
             // chunks that intersect the matrix (TMA clips a partial last one)
             const uint32_t n_left = p.n - n0;

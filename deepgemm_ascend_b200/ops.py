@@ -12,7 +12,8 @@ import torch
 from . import _lib
 from ._lib import lib, check
 
-_DTYPE_TO_ACL = {torch.float32: _lib.ACL_FLOAT, torch.float16: _lib.ACL_FLOAT16, torch.bfloat16: _lib.ACL_BF16}
+_DTYPE_TO_ACL = {torch.float32: _lib.ACL_FLOAT, torch.float16: _lib.ACL_FLOAT16, torch.bfloat16: _lib.ACL_BF16,
+                 torch.int32: _lib.ACL_INT32}
 if hasattr(torch, "float8_e4m3fn"):
     _DTYPE_TO_ACL[torch.float8_e4m3fn] = _lib.ACL_FLOAT8_E4M3FN
 
@@ -154,6 +155,23 @@ def nshard_range(n, world_size, rank):
     b, c = ctypes.c_uint32(0), ctypes.c_uint32(0)
     check(lib.dgaNShardRange(n, world_size, rank, ctypes.byref(b), ctypes.byref(c)), "dgaNShardRange")
     return b.value, c.value
+
+
+# ---- M-grouped contiguous matmul (MoE; DeepGEMM m_grouped_gemm_nt_contiguous semantics) -------------------------
+def m_grouped_matmul(self, weight, group_index, out=None, stream=None):
+    """out[i,:] = self[i,:] @ weight[group_index[i]].T; self [M_total,K], weight [G,N,K], group_index int32 [M_total]
+    (constant over every 128-row block, -1 = padding block left unwritten), M_total % 128 == 0."""
+    _require_cuda(self, weight, group_index)
+    if out is None:
+        out = torch.empty((self.shape[0], weight.shape[1]), dtype=self.dtype, device=self.device)
+    ws = ctypes.c_uint64(0)
+    ex = ctypes.c_void_p(None)
+    a, w, g, c = acl_tensor(self), acl_tensor(weight), acl_tensor(group_index), acl_tensor(out)
+    check(lib.dgaMGroupedMatmulGetWorkspaceSize(ctypes.byref(a), ctypes.byref(w), ctypes.byref(g), ctypes.byref(c),
+                                                ctypes.byref(ws), ctypes.byref(ex)),
+          "dgaMGroupedMatmulGetWorkspaceSize")
+    check(lib.dgaMGroupedMatmul(ctypes.c_void_p(None), 0, ex, _stream_ptr(stream)), "dgaMGroupedMatmul")
+    return out
 
 
 # ---- fp8 e4m3 block-scaled (DeepGEMM semantics; not in the reference) -------------------------------------------

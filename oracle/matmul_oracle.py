@@ -202,6 +202,21 @@ def fp8_block_scaled_golden(a_codes, a_sf, w_codes, w_sf):
 
 
 # --- framework host math ------------------------------------------------------------------------------------
+def m_grouped_golden_fp64(a, w, group_index):
+    """M-grouped contiguous matmul (MoE): out[i,:] = a[i,:] . w[group_index[i]]^T in fp64; rows whose index is
+    negative are padding and come back as NaN (the device leaves them unwritten).  Not in the reference; semantics of
+    upstream deepseek-ai/DeepGEMM `m_grouped_*_gemm_nt_contiguous` (a [M_total,K], b [G,N,K], m_indices [M_total]);
+    parity unpinned by the reference, anchored on the fp64 rule of north_star."""
+    a64, w64 = a.astype(np.float64), w.astype(np.float64)
+    out = np.full((a.shape[0], w.shape[1]), np.nan, dtype=np.float64)
+    for g in np.unique(group_index):
+        if g < 0:
+            continue
+        rows = np.nonzero(group_index == g)[0]
+        out[rows] = a64[rows] @ w64[g].T
+    return out
+
+
 def align16(x):
     return (x + 15) & ~15
 

@@ -115,6 +115,39 @@ def test_config2_sampled_rows(dga):
     assert np.max(np.abs(got.astype(np.float64).sum(axis=1) - row_sum) / row_sum) < 2e-4
 
 
+def _sampled_full_size(dga, m, n, k, seed):
+    """Full-size case generated on the device (the reference's U[1,10] distribution), checked on sampled rows against
+    the fp64 oracle and over the whole output through the row-sum identity sum_j C[i,j] == A[i,:] . (B 1)."""
+    gen = torch.Generator(device=DEV).manual_seed(seed)
+    a = (torch.rand((m, k), device=DEV, generator=gen) * 9 + 1).to(torch.bfloat16)
+    w = (torch.rand((n, k), device=DEV, generator=gen) * 9 + 1).to(torch.bfloat16)   # weight stored [N,K]
+    out = torch.empty((m, n), dtype=torch.bfloat16, device=DEV)
+    before = dga.kernel_launch_count()
+    dga.catlass_dynamic_matmul(a, w.t(), out=out)
+    torch.cuda.synchronize()
+    assert dga.kernel_launch_count() > before
+    rows = np.random.RandomState(seed).choice(m, min(m, 48), replace=False)
+    rows_t = torch.from_numpy(rows).to(DEV)
+    w_host = w.float().cpu().numpy()
+    ref = orc.golden_fp64(a[rows_t].float().cpu().numpy(), w_host.T)
+    assert orc.max_rel_err(out[rows_t].float().cpu().numpy(), ref) <= 2.0 ** -7
+    w_sum = w_host.astype(np.float64).sum(axis=0)                      # B 1, exact in fp64
+    row_sum = a.double().cpu().numpy() @ w_sum
+    got_sum = out.double().sum(dim=1).cpu().numpy()
+    assert np.max(np.abs(got_sum - row_sum) / row_sum) < 2e-4
+
+
+@pytest.mark.parametrize("m", [512, 2048, 8192])
+def test_config3_sweep_full_size(dga, m):
+    """BASELINE config 3, the prefill end of the dynamic-M sweep at N=4096, K=7168 (decode points are in ACLNN_CASES)."""
+    _sampled_full_size(dga, m, 4096, 7168, seed=m)
+
+
+def test_config5_one_shard_full_size(dga):
+    """BASELINE config 5 as one rank of eight sees it: M=16384, N=57344/8, K=7168."""
+    _sampled_full_size(dga, 16384, 7168, 7168, seed=5)
+
+
 def test_golden_vectors_framework_path(dga, golden_dir):
     """run_mmad_bench (fp16 -> fp32) on the reference's own generated vectors (gen_golden.py run with a seed)."""
     z = np.load(os.path.join(golden_dir, "numeric_uniform.npz"))
@@ -255,3 +288,62 @@ def test_framework_path_odd_shapes(dga):
         ok, ratio = orc.verify_result(z.cpu().numpy(), golden, rtol=orc.RTOL_TEST)
         assert ok, ((m, n, k), ratio)
         assert orc.max_rel_err(z.cpu().numpy(), orc.golden_fp64(x1, x2)) < 1e-5
+
+
+# ---- batched framework launch and the M-grouped contiguous matmul ------------------------------------
+def test_rtc_batched_single_launch(dga):
+    """run_mmad_rtc with batch > 1 and aligned pitches is ONE launch (3-D tensor maps), ragged m and n per entry."""
+    rng = np.random.default_rng(7)
+    b, m, n, k = 5, 200, 328, 264
+    x = torch.from_numpy(orc.heavy_tail(rng, [b, m, k])).to(DEV).to(torch.bfloat16)
+    y = torch.from_numpy(orc.heavy_tail(rng, [b, k, n])).to(DEV).to(torch.bfloat16)
+    out = torch.zeros((b, m, n), dtype=torch.float32, device=DEV)
+    before = dga.kernel_launch_count()
+    dga.run_mmad_rtc(x, y, out)
+    assert dga.kernel_launch_count() - before == 1
+    for i in range(b):
+        ref = orc.golden_fp64(x[i].float().cpu().numpy(), y[i].float().cpu().numpy())
+        assert orc.max_rel_err(out[i].cpu().numpy(), ref) < 1e-5
+
+
+@pytest.mark.parametrize("groups,n,k,dtype", [(4, 512, 256, torch.bfloat16), (8, 1000, 520, torch.bfloat16),
+                                                (3, 384, 1024, torch.float16)])
+def test_m_grouped_matmul_matches_oracle(dga, groups, n, k, dtype):
+    rng = np.random.RandomState(groups + n + k)
+    blocks = rng.randint(0, 4, size=groups)          # 128-row blocks per group; some groups are empty
+    blocks[0] = max(blocks[0], 1)
+    index = []
+    for g, nb in enumerate(blocks):
+        index += [g] * (128 * nb)
+        if g % 2 == 1:
+            index += [-1] * 128                       # a padding block between groups
+    index = np.array(index, dtype=np.int32)
+    m_total = index.size
+    a, _ = _inputs(m_total, 8, k, dtype, seed=1)
+    w = np.stack([_inputs(8, n, k, dtype, seed=10 + g)[1].T for g in range(groups)])   # [G, N, K]
+    ta, tw = _to_dev(a, dtype), _to_dev(w, dtype)
+    out = torch.full((m_total, n), 768.0, dtype=dtype, device=DEV)
+    before = dga.kernel_launch_count()
+    dga.m_grouped_matmul(ta, tw, torch.from_numpy(index).to(DEV), out=out)
+    torch.cuda.synchronize()
+    assert dga.kernel_launch_count() - before == 1
+    got = out.float().cpu().numpy()
+    ref = orc.m_grouped_golden_fp64(a, w, index)
+    live = index >= 0
+    assert orc.max_rel_err(got[live], ref[live]) <= (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7)
+    assert np.all(got[~live] == 768.0)               # padding blocks are left untouched
+
+
+def test_m_grouped_matmul_deepseek_shape(dga):
+    """MoE up-projection class shape: 8 experts x 512 rows, N=4096, K=7168, sampled rows against fp64."""
+    g, per, n, k = 8, 512, 4096, 7168
+    gen = torch.Generator(device=DEV).manual_seed(3)
+    a = (torch.rand((g * per, k), device=DEV, generator=gen) * 9 + 1).to(torch.bfloat16)
+    w = (torch.rand((g, n, k), device=DEV, generator=gen) * 9 + 1).to(torch.bfloat16)
+    index = torch.arange(g, device=DEV, dtype=torch.int32).repeat_interleave(per)
+    out = dga.m_grouped_matmul(a, w, index)
+    torch.cuda.synchronize()
+    rows = np.random.RandomState(0).choice(g * per, 24, replace=False)
+    for r in rows:
+        ref = orc.golden_fp64(a[r:r + 1].float().cpu().numpy(), w[r // per].float().cpu().numpy().T)
+        assert orc.max_rel_err(out[r:r + 1].float().cpu().numpy(), ref) <= 2.0 ** -7
