@@ -13,6 +13,7 @@ Workloads (BASELINE.json configs):
   m<M>               bf16 M in {1,16,...} at N=4096 K=7168 (dynamic-M sweep point; CUDA-graph of 20 launches per step)
   fp8                e4m3 block-scaled M=4096 N=7168 K=16384, UE8M0 (power-of-two) scales -> tensor-core block scaling
   fp8_fp32scales     same shape, arbitrary fp32 scales -> software promotion kernel
+  moe                M-grouped contiguous bf16 (8 experts x 1024 rows, N=4096, K=7168; SURVEY 8(f) f4, not a BASELINE config)
 Timing: CUDA events on the launching stream, K timed steps after W >= 3 warm-ups, barrier + synchronize on both
 sides, max over ranks. Buffers rotate over enough distinct (A, B, C) sets to exceed 2x the 126 MB L2.
 The oracle (oracle/) is used only for the cpu_baseline leg and for --impl reference.
@@ -52,6 +53,8 @@ def workload_shape(name, world):
         return dict(m=16384, n=57344 // world, k=7168, dtype="bf16", n_total=57344, scaling="strong")
     if name in ("fp8", "fp8_fp32scales"):
         return dict(m=4096, n=7168, k=16384, dtype="fp8", n_total=7168 * world, scaling="weak")
+    if name == "moe":
+        return dict(m=8192, n=4096, k=7168, dtype="bf16", n_total=4096 * world, scaling="weak", groups=8)
     if name.startswith("m") and name[1:].isdigit():
         return dict(m=int(name[1:]), n=4096, k=7168, dtype="bf16", n_total=4096 * world, scaling="weak")
     raise SystemExit("unknown workload %s" % name)
@@ -65,7 +68,7 @@ def algorithmic(shape):
         kb, nb = -(-k // 128), -(-n // 128)
         nbytes = m * k + n * k + 2 * m * n + 4 * m * kb + 4 * nb * kb
     else:
-        nbytes = 2.0 * (m * k + n * k + m * n)
+        nbytes = 2.0 * (m * k + shape.get("groups", 1) * n * k + m * n)   # moe: every expert's weight is read once
     return flops, float(nbytes)
 
 

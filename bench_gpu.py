@@ -54,8 +54,16 @@ def run_ours(args, rank, world):
         a_bufs = [torch.randn((m, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
         w_bufs = [torch.randn((n, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]  # [N,K]
         c_bufs = [torch.empty((m, n), device=dev, dtype=torch.bfloat16) for _ in range(sets)]
-        execs = [dga.Executor(a_bufs[i], w_bufs[i].t(), c_bufs[i]) for i in range(sets)]   # phase 1, once per set
+        if args.workload == "moe":
+            g = shape["groups"]
+            w_bufs = [torch.randn((g, n, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
+            index = torch.arange(g, device=dev, dtype=torch.int32).repeat_interleave(m // g)
+            execs = [dga.MGroupedExecutor(a_bufs[i], w_bufs[i], index, c_bufs[i]) for i in range(sets)]
+        else:
+            execs = [dga.Executor(a_bufs[i], w_bufs[i].t(), c_bufs[i]) for i in range(sets)]   # phase 1, once per set
     plan = dga.select_kernel(m, n, k, use_cache=True) if not fp8 else {"kernelSerial": 0}
+    if args.workload == "moe":
+        plan = {"kernelSerial": 0, "ctaGroup": 1, "m1": 128}
 
     stream = torch.cuda.current_stream()
     graph = None
@@ -121,7 +129,8 @@ def run_ours(args, rank, world):
     value = flops * n_launch * world / (total_ms_max * 1e-3) / 1e12
 
     # ---- e2e: host buffers in, host buffer out, through the public operator call
-    e2e = e2e_run(dga, dev, m, n, k, steps=max(3, min(args.steps, 20)), flops=flops, world=world, dist=dist, fp8=fp8)
+    e2e = e2e_run(dga, dev, m, n, k, steps=max(3, min(args.steps, 20)), flops=flops, world=world, dist=dist, fp8=fp8,
+                  groups=shape.get("groups", 0))
 
     # ---- optional: all-gather of C over NVLink (only when the caller needs the full output)
     gather = None
@@ -178,7 +187,7 @@ def run_ours(args, rank, world):
         dist.destroy_process_group()
 
 
-def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False):
+def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False, groups=0):
     """Same metric end to end: every step copies its A and W from pinned host memory to the device, calls the
     operator and copies C back to pinned host memory, all inside the timed region.  The three legs run on three
     streams over a ring of 2 device buffer sets, so the copies of step i+1 and i-1 overlap the GEMM of step i
@@ -186,7 +195,8 @@ def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False):
     in_dtype = torch.float8_e4m3fn if fp8 else torch.bfloat16
     depth = 2
     ha = torch.randn((m, k)).to(in_dtype).pin_memory()
-    hw = torch.randn((n, k)).to(in_dtype).pin_memory()
+    hw = torch.randn((groups, n, k) if groups else (n, k)).to(in_dtype).pin_memory()
+    index = torch.arange(groups, device=dev, dtype=torch.int32).repeat_interleave(m // groups) if groups else None
     hc = [torch.empty((m, n), dtype=torch.bfloat16).pin_memory() for _ in range(depth)]
     da = [torch.empty_like(ha, device=dev) for _ in range(depth)]
     dw = [torch.empty_like(hw, device=dev) for _ in range(depth)]
@@ -219,6 +229,8 @@ def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False):
             s_mm.wait_event(out_done[i])         # the copy-out that last read this slot's C
             if fp8:
                 dga.fp8_block_scaled_matmul(da[i], dsa[i], dw[i], dsw[i], out=dc[i])
+            elif groups:
+                dga.m_grouped_matmul(da[i], dw[i], index, out=dc[i])
             else:
                 dga.catlass_dynamic_matmul(da[i], dw[i].t(), out=dc[i])     # two-phase C ABI underneath
             mm_done[i].record(s_mm)

@@ -174,6 +174,37 @@ def m_grouped_matmul(self, weight, group_index, out=None, stream=None):
     return out
 
 
+class MGroupedExecutor:
+    """Repeatable grouped-matmul plan: phase 1 once, phase 2 per call."""
+
+    def __init__(self, self_t, weight, group_index, out):
+        _require_cuda(self_t, weight, group_index, out)
+        self._keep = (self_t, weight, group_index, out)
+        ws = ctypes.c_uint64(0)
+        ex = ctypes.c_void_p(None)
+        a, w, g, c = acl_tensor(self_t), acl_tensor(weight), acl_tensor(group_index), acl_tensor(out)
+        check(lib.dgaMGroupedMatmulGetWorkspaceSize(ctypes.byref(a), ctypes.byref(w), ctypes.byref(g), ctypes.byref(c),
+                                                    ctypes.byref(ws), ctypes.byref(ex)),
+              "dgaMGroupedMatmulGetWorkspaceSize")
+        check(lib.dgaSetExecutorRepeatable(ex), "dgaSetExecutorRepeatable")
+        self._ex = ex
+
+    def __call__(self, stream=None):
+        check(lib.dgaMGroupedMatmul(ctypes.c_void_p(None), 0, self._ex, _stream_ptr(stream)), "dgaMGroupedMatmul")
+        return self._keep[3]
+
+    def close(self):
+        if self._ex is not None:
+            destroy_executor(self._ex)
+            self._ex = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 # ---- fp8 e4m3 block-scaled (DeepGEMM semantics; not in the reference) -------------------------------------------
 def fp8_get_workspace_size(a, a_scale, mat2, w_scale, out):
     ws = ctypes.c_uint64(0)
