@@ -20,6 +20,7 @@
 #include "gemm_smallm_sm100.cuh"
 #include "gemm_fp8_sm100.cuh"
 #include "repack_sm100.cuh"
+#include "splitk_reduce_sm100.cuh"
 #include "tile_selector.h"
 
 namespace dga {
@@ -133,10 +134,13 @@ struct DenseLaunch {
     } eff{}, enc{};          // enc: what the tensor maps below were encoded for
     CUtensorMap tm_a, tm_b, tm_d;
     bool encoded = false;
-    bool maps_fresh() const { return encoded && std::memcmp(&eff, &enc, sizeof(Operands)) == 0; }
+    bool maps_fresh() const {
+        return encoded && std::memcmp(&eff, &enc, sizeof(Operands)) == 0 && split_ws == split_ws_enc;
+    }
     // kModeBatched: `batch` independent GEMMs of one shape, slabs `slab_*` elements apart.
     // kModeMGrouped: plan.m = M_total rows in 128-row blocks, weight [groups, N, K], group_index[M_total] on the device.
     int mode = kModePlain;
+    void* split_ws = nullptr, *split_ws_enc = nullptr;   // fp32 partial slabs of the multicore split-K variant
     uint32_t batch = 1, groups = 0;
     uint64_t slab_a = 0, slab_b = 0, slab_d = 0;
     const int32_t* group_index = nullptr;
@@ -219,6 +223,18 @@ static int launch_common_out(const DenseLaunch& L, const GemmParams& gp, cudaStr
 static int encode_common(DenseLaunch& L) {
     const DgaTilingPlan& p = L.plan;
     const uint32_t cta = p.ctaGroup, load_n = p.n1 / cta;
+    if (L.mode == kModeSplitK) {
+        int rcs = make_tmap_2d(&L.tm_a, L.eff.a, p.dtype, p.k, p.m, L.eff.lda, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rcs != ACLNN_SUCCESS) return rcs;
+        if (p.layoutTagB == 1)
+            rcs = make_tmap_2d(&L.tm_b, L.eff.b, p.dtype, p.k, p.n, L.eff.ldb, 64, load_n, CU_TENSOR_MAP_SWIZZLE_128B);
+        else
+            rcs = make_tmap_2d(&L.tm_b, L.eff.b, p.dtype, p.n, p.k, L.eff.ldb, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rcs != ACLNN_SUCCESS) return rcs;
+        const uint64_t pitch = splitk_ws_pitch(p.n);
+        return make_tmap_3d(&L.tm_d, L.split_ws, ACL_FLOAT, p.n, p.m, p.splitkFactor, pitch, uint64_t(p.m) * pitch, 32, 128,
+                            CU_TENSOR_MAP_SWIZZLE_128B);
+    }
     if (L.mode != kModePlain) {
         const uint32_t epi3 = epi_cols_for(p.n1, elem_bytes(p.outDtype));
         const CUtensorMapSwizzle d_swz3 = epi3 * elem_bytes(p.outDtype) == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
@@ -259,13 +275,40 @@ static int encode_common(DenseLaunch& L) {
     return make_tmap_2d(&L.tm_d, L.eff.d, p.outDtype, p.n, p.m, L.eff.ldd, epi, 128, d_swz);
 }
 
+template <typename OutT>
+static int launch_splitk_reduce(const DenseLaunch& L, cudaStream_t stream) {
+    const DgaTilingPlan& p = L.plan;
+    const uint32_t pitch = splitk_ws_pitch(p.n);
+    const uint64_t groups = uint64_t(p.m) * ((p.n + 3) / 4);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(uint32_t(std::min<uint64_t>((groups + kReduceThreads - 1) / kReduceThreads, 148 * 8)));
+    cfg.blockDim = dim3(kReduceThreads);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    fill_launch_attrs(cfg, attr, 1);
+    DGA_CUDA(cudaLaunchKernelEx(&cfg, splitk_reduce_kernel<OutT>, static_cast<const float*>(L.split_ws),
+                                uint64_t(p.m) * pitch, pitch, static_cast<OutT*>(L.eff.d), L.eff.ldd, p.m, p.n,
+                                uint32_t(p.splitkFactor)));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return ACLNN_SUCCESS;
+}
+
 static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     const DgaTilingPlan& p = L.plan;
+    if (p.kernelSerial == DGA_KERNEL_SPLITK_REDUCE) {
+        if (L.mode != kModePlain && L.mode != kModeSplitK) {
+            set_error("split-K is not combined with batched / grouped launches");
+            return ACLNN_ERR_INNER_TILING_ERROR;
+        }
+        L.mode = kModeSplitK;
+        L.split_ws = workspace;
+    }
     if (!L.maps_fresh()) {
         int rc = encode_common(L);
         if (rc != ACLNN_SUCCESS) return rc;
         L.encoded = true;
         L.enc = L.eff;
+        L.split_ws_enc = L.split_ws;
     }
     const uint32_t cta = p.ctaGroup;
     GemmParams gp{};
@@ -308,6 +351,26 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
     gp.debug = dbg;
     if (dbg & 16) gp.trace = trace_buffer();
+    if (L.mode == kModeSplitK) {
+        gp.split_k = p.splitkFactor;
+        gp.dp_tiles *= p.splitkFactor;
+        gp.epi_cols = 32;
+        int rcs;
+        if (cta == 2)
+            rcs = p.layoutTagB == 1 ? launch_common_inst<2, float, false, kModeSplitK>(L, gp, stream)
+                                    : launch_common_inst<2, float, true, kModeSplitK>(L, gp, stream);
+        else
+            rcs = p.layoutTagB == 1 ? launch_common_inst<1, float, false, kModeSplitK>(L, gp, stream)
+                                    : launch_common_inst<1, float, true, kModeSplitK>(L, gp, stream);
+        if (rcs != ACLNN_SUCCESS) return rcs;
+        switch (p.outDtype) {
+            case ACL_BF16: return launch_splitk_reduce<__nv_bfloat16>(L, stream);
+            case ACL_FLOAT16: return launch_splitk_reduce<__half>(L, stream);
+            case ACL_FLOAT: return launch_splitk_reduce<float>(L, stream);
+        }
+        set_error("unsupported output dtype");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
     if (L.mode != kModePlain) {
         // single-CTA tiles only; the instances the two callers need: the framework's batched fp32-output GEMM over
         // row-major B, and the MoE grouped GEMM over [G,N,K] weights with a 16-bit output
@@ -401,8 +464,9 @@ static int launch_variant(DenseLaunch& L, cudaStream_t stream, void* workspace) 
         case DGA_KERNEL_SMALL:
         case DGA_KERNEL_PADDING_COMMON: return launch_common(L, stream, nullptr);
         case DGA_KERNEL_STREAMK:
+        case DGA_KERNEL_SPLITK_REDUCE:
             if (workspace == nullptr) {
-                set_error("the stream-K variant needs its workspace");
+                set_error("the stream-K / split-K variants need their workspace");
                 return ACLNN_ERR_PARAM_INVALID;
             }
             return launch_common(L, stream, workspace);

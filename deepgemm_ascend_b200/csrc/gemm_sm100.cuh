@@ -59,7 +59,10 @@ struct GemmParams {
     unsigned long long* trace; // debug & 16: per CTA {t_start, t_first_data, t_last_mma_issued, t_end (ns), clk_start, clk_end}
     // kMode 1 (batched: A [B,M,K], B [B,K,N] or [B,N,K], D [B,M,N], 3-D tensor maps): tiles per batch entry
     // kMode 2 (M-grouped contiguous: A [M_total,K], B [G,N,K], D [M_total,N]): group of every row, -1 = skip
+    // kMode 3 (split-K: work item = K slice `i % split_k` of tile `i / split_k`; fp32 partial tiles go to slab
+    //         [slice] of a [split_k, M, N] workspace behind a 3-D tensor map, splitk_reduce_kernel adds them up)
     uint32_t tiles_per_batch;
+    uint32_t split_k;
     const int32_t* group_index;
     float* sk_partials;      // [cluster][head/tail][cta rank][128][block_n] fp32
     int32_t* sk_sems;        // [sk tile][cta rank] arrival counters, zero on entry and on exit
@@ -227,7 +230,25 @@ __host__ __device__ inline SmemLayout make_smem_layout(uint32_t d_stage_bytes, u
 // tile index carries the batch entry, 3-D tensor maps clip ragged M/N per entry); 2 M-grouped contiguous (MoE:
 // every 128-row block of A multiplies the weight of its group; rows of one block share a group, -1 skips it).
 // Modes 1 and 2 run single-CTA tiles (a CTA pair would have to share one B tile across two row blocks).
-constexpr int kModePlain = 0, kModeBatched = 1, kModeMGrouped = 2;
+// kMode 3: multicore split-K (the reference declares it as kernel type 3, catlass_dynamic_matmul_tiling_key.h:117-130,
+// and never dispatches it) for shapes whose tiles fill well under one wave: every tile's K range is cut into
+// split_k slices that run as independent work items; see splitk_reduce_sm100.cuh for the second half.
+constexpr int kModePlain = 0, kModeBatched = 1, kModeMGrouped = 2, kModeSplitK = 3;
+// Turns the iterator's item into (tile, K-block range, slab = third coordinate of the 3-D maps).
+template <int kMode>
+__device__ __forceinline__ void resolve_item(const GemmParams& p, WorkItem& w, uint32_t& slab) {
+    if constexpr (kMode == kModeBatched) {
+        slab = w.tile / p.tiles_per_batch;
+        w.tile -= slab * p.tiles_per_batch;
+    } else if constexpr (kMode == kModeSplitK) {
+        slab = w.tile % p.split_k;
+        w.tile /= p.split_k;
+        w.kb0 = static_cast<uint32_t>(static_cast<uint64_t>(slab) * p.k_blocks / p.split_k);
+        w.kb1 = static_cast<uint32_t>(static_cast<uint64_t>(slab + 1) * p.k_blocks / p.split_k);
+    } else {
+        slab = 0;
+    }
+}
 template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
@@ -235,7 +256,9 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                   const __grid_constant__ CUtensorMap tm_sfb, const __grid_constant__ PeerMaps peers,
                   const GemmParams p) {
     static_assert(!(kMx && kBMn), "block-scaled fp8 wants K-major operands");
-    static_assert(kMode == kModePlain || (kCta == 1 && !kMx), "batched / grouped modes are single-CTA, 16-bit");
+    static_assert(kMode == kModePlain || kMode == kModeSplitK || (kCta == 1 && !kMx),
+                  "batched / grouped modes are single-CTA, 16-bit");
+    static_assert(kMode != kModeSplitK || (sizeof(OutT) == 4 && !kMx), "split-K slices leave fp32 partial tiles");
     ptx::grid_dep_launch();   // the next grid on the stream may set itself up while this one runs
     const bool tracing = (p.debug & 16) != 0 && p.trace != nullptr;
     if (tracing && threadIdx.x == 0) {
@@ -305,14 +328,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         WorkIter it(p, cluster_id, num_clusters);
         WorkItem w;
         while (it.next(w)) {
-            uint32_t mb, nb;
-            int32_t z = 0;   // third tensor-map coordinate: batch entry (mode 1) or group (mode 2)
-            if constexpr (kMode == kModeBatched) {
-                z = static_cast<int32_t>(w.tile / p.tiles_per_batch);
-                tile_coords(p, w.tile - z * p.tiles_per_batch, mb, nb);
-            } else {
-                tile_coords(p, w.tile, mb, nb);
-            }
+            uint32_t mb, nb, slab;
+            resolve_item<kMode>(p, w, slab);
+            int32_t z = static_cast<int32_t>(slab);   // third tensor-map coordinate: batch entry (mode 1) or group (mode 2)
+            tile_coords(p, w.tile, mb, nb);
             const int32_t m_idx = static_cast<int32_t>(mb * (kBlockM * kCta) + cta_rank * kBlockM);
             const int32_t n_idx = static_cast<int32_t>(nb * p.block_n + cta_rank * load_n);
             if constexpr (kMode == kModeMGrouped) {
@@ -364,13 +383,14 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                         else ptx::tma_load_2d(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
                         if constexpr (kBMn) {
                             for (uint32_t j = 0; j < load_n / 64; ++j) {
-                                if constexpr (kMode == kModePlain)
+                                if constexpr (kMode == kModePlain || kMode == kModeSplitK)
                                     ptx::tma_load_2d(&tm_b, &full_bar[stage], sb + j * 8192, n_idx + j * 64, k_idx);
                                 else
                                     ptx::tma_load_3d(&tm_b, &full_bar[stage], sb + j * 8192, n_idx + j * 64, k_idx, z);
                             }
                         } else {
-                            if constexpr (kMode == kModePlain) ptx::tma_load_2d(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
+                            if constexpr (kMode == kModePlain || kMode == kModeSplitK)
+                                ptx::tma_load_2d(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
                             else ptx::tma_load_3d(&tm_b, &full_bar[stage], sb, k_idx, n_idx, z);
                         }
                         ptx::mbar_arrive_expect_tx(&full_bar[stage], L.a_stage_bytes + L.b_stage_bytes + sf_bytes);
@@ -401,6 +421,8 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
             WorkIter it(p, cluster_id, num_clusters);
             WorkItem w;
             for (; it.next(w); ++iter) {
+                uint32_t slab_unused;
+                resolve_item<kMode>(p, w, slab_unused);
                 if constexpr (kMode == kModeMGrouped) {
                     uint32_t mb, nb;
                     tile_coords(p, w.tile, mb, nb);
@@ -473,7 +495,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
             if (epi_tid == 0) {
                 const int32_t c0 = static_cast<int32_t>(col - half * kEpiCols);
                 if (m0 < p.m && !(p.debug & 4)) {
-                    if constexpr (kMode == kModeBatched)
+                    if constexpr (kMode == kModeBatched || kMode == kModeSplitK)
                         ptx::tma_store_3d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes, c0, static_cast<int32_t>(m0), zb);
                     else
                         ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes, c0, static_cast<int32_t>(m0));
@@ -488,13 +510,10 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         WorkIter it(p, cluster_id, num_clusters);
         WorkItem w;
         for (; it.next(w); ++iter) {
-            uint32_t mb, nb;
-            if constexpr (kMode == kModeBatched) {
-                zb = static_cast<int32_t>(w.tile / p.tiles_per_batch);
-                tile_coords(p, w.tile - zb * p.tiles_per_batch, mb, nb);
-            } else {
-                tile_coords(p, w.tile, mb, nb);
-            }
+            uint32_t mb, nb, slab;
+            resolve_item<kMode>(p, w, slab);
+            zb = static_cast<int32_t>(slab);
+            tile_coords(p, w.tile, mb, nb);
             const uint32_t m0 = mb * (kBlockM * kCta) + cta_rank * kBlockM;
             const uint32_t n0 = nb * p.block_n;
             if constexpr (kMode == kModeMGrouped) {
@@ -513,7 +532,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                 if constexpr (kCta == 2) ptx::mbar_arrive_remote(&tmem_empty_bar[as], 0);
                 else ptx::mbar_arrive(&tmem_empty_bar[as]);
             };
-            if (w.kb1 - w.kb0 == p.k_blocks) {
+            if (kMode == kModeSplitK || w.kb1 - w.kb0 == p.k_blocks) {
                 for (uint32_t c = 0; c < chunks; ++c) {
                     uint32_t v[32];
                     ptx::tmem_ld_32x32(taddr + c * kEpiCols, v);

@@ -228,7 +228,9 @@ int finalize_plan(DgaTilingPlan& p) {
         }
         p.m1 = static_cast<uint16_t>(128 * cta);
         p.k1 = static_cast<uint16_t>(128 / in_b);
-        const uint32_t fixed = 2 * 128 * epi_cols_host(p.n1, out_b) * out_b + 1024 + 256;
+        const bool split_reduce = p.kernelSerial == DGA_KERNEL_SPLITK_REDUCE;
+        const uint32_t epi_b = split_reduce ? 4u : out_b;   // split-K slices leave fp32 partial tiles
+        const uint32_t fixed = 2 * 128 * epi_cols_host(p.n1, epi_b) * epi_b + 1024 + 256;
         const uint32_t cap = max_stages(128 * 128 + (p.n1 / cta) * 128, fixed, hw.smemBytes, 12);
         if (p.stages == 0 || p.stages > cap) p.stages = static_cast<uint8_t>(cap);
         if (p.stages < 2) {
@@ -237,9 +239,18 @@ int finalize_plan(DgaTilingPlan& p) {
         }
         const uint32_t tiles = ceil_div(p.m, 128 * cta) * ceil_div(p.n, p.n1);
         p.blockDim = std::min(tiles, hw.smCount / cta) * cta;
-        p.smemBytes = common_smem_bytes(p.n1, cta, p.stages, out_b, in_b);
+        p.smemBytes = common_smem_bytes(p.n1, cta, p.stages, epi_b, in_b);
         p.workspaceBytes = 0;
-        if (p.kernelSerial == DGA_KERNEL_STREAMK) {
+        if (split_reduce) {
+            const uint32_t kb = ceil_div(p.k, 128 / in_b);
+            if (p.splitkFactor < 2 || p.splitkFactor > 16 || p.splitkFactor > kb) {
+                set_error("split-K needs 2 <= splitkFactor <= min(16, K blocks)");
+                return ACLNN_ERR_INNER_TILING_ERROR;
+            }
+            p.blockDim = uint32_t(std::min<uint64_t>(uint64_t(tiles) * p.splitkFactor, hw.smCount / cta)) * cta;
+            p.workspaceBytes = splitk_ws_bytes(p.m, p.n, p.splitkFactor);
+            p.paddingTagC = 0;   // the reduce kernel stores C with plain st.global: any pitch will do
+        } else if (p.kernelSerial == DGA_KERNEL_STREAMK) {
             const uint32_t clusters = hw.smCount / cta;
             uint32_t dp, sk;
             streamk_split(tiles, clusters, ceil_div(p.k, 128 / in_b), dp, sk);

@@ -51,6 +51,12 @@ void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t& dp,
 // Workspace layout of the stream-K variant: fp32 partial slots, then the per-tile arrival counters.
 uint64_t streamk_partial_bytes(uint32_t clusters, uint32_t cta_group, uint32_t block_n);
 
+// Multicore split-K (DGA_KERNEL_SPLITK_REDUCE): row pitch (floats) and bytes of the [split][m][pitch] fp32 partial slabs.
+inline uint32_t splitk_ws_pitch(uint32_t n) { return round_up(n, 32); }
+inline uint64_t splitk_ws_bytes(uint32_t m, uint32_t n, uint32_t split) {
+    return uint64_t(split) * m * splitk_ws_pitch(n) * 4;
+}
+
 // Stride repack (role of PaddingWorkspaceSize, op_kernel/kernel/kernel_utils.h:63-75, and of the workspace carve-up
 // padA | padB | padC in padding_common_matmul_kernel.h:77-82): operands whose paddingTag is set are copied to the
 // front of the workspace with a 128-byte-multiple row pitch; whatever else the variant needs (stream-K partials)
