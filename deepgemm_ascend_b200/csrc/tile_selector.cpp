@@ -329,11 +329,27 @@ int select_kernel(DgaTilingPlan& p) {
     // measured on B200 (N=4096, K=7168): the swap-AB kernel also wins at M = 128 (17.7 vs 28.9 us); the estimates
     // are too coarse there, so the rule is explicit.  Beyond 128 rows the fp32 reduction slots (m x 512 B per CTA)
     // crowd out the ring and the estimates decide.
+    // Multicore split-K + reduce kernel (the reference's declared kernel type 3): when even 256 x 256 pair tiles fill
+    // at most a quarter of the CTA pairs and K is long, cutting K gives every pair a slice of a wide tile instead of
+    // leaving most SMs idle behind narrow ones.  Measured on B200 (profiles/r01_splitk_reduce_sweep.log): M=256,
+    // N=4096, K=7168: 25.2 vs 27.9 us; M=256, N=2048: 16.4 vs 27.2 us; with more tiles than that it loses
+    // (M=512, N=4096: 38.5 vs 29.3 us), hence the explicit rule.
+    const uint32_t pairs = platform().smCount / 2;
+    const uint32_t tiles256 = ceil_div(p.m, 256) * ceil_div(p.n, 256);
+    const uint32_t kb_all = ceil_div(p.k, 128 / in_b);
+    const uint32_t split_r = std::min<uint32_t>(std::min<uint32_t>(8, pairs / std::max(1u, tiles256)), kb_all / 14);
     if (sbest.split != 0 && (sbest.us < best.us || p.m <= 128)) {
         p.kernelSerial = DGA_KERNEL_SPLITK;
         p.splitkFactor = static_cast<uint16_t>(sbest.split);
         p.stages = static_cast<uint8_t>(sbest.stages);
         p.estTimeUs = sbest.us;
+    } else if (p.m > 128 && tiles256 * 4 <= pairs && split_r >= 2) {
+        p.kernelSerial = DGA_KERNEL_SPLITK_REDUCE;
+        p.ctaGroup = 2;
+        p.n1 = 256;
+        p.stages = 0;
+        p.splitkFactor = static_cast<uint16_t>(split_r);
+        p.estTimeUs = best.us;
     } else {
         fill_common(p, best);
     }
