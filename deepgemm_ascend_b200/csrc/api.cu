@@ -30,6 +30,7 @@ static std::atomic<uint64_t> g_launches{0};
 static std::atomic<int64_t> g_opt_splitk_prefetch{-1};
 static std::atomic<int64_t> g_opt_pdl{-1};
 static std::atomic<int64_t> g_opt_splitk_batch{-1};
+static std::atomic<int64_t> g_opt_raster{-1};   // raster_group override (sweeps)
 
 #define DGA_CUDA(expr)                                                                       \
     do {                                                                                     \
@@ -319,6 +320,7 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     gp.num_m_blocks = ceil_div(p.m, 128 * cta);
     gp.num_n_blocks = ceil_div(p.n, p.n1);
     gp.raster_group = p.swizzleOffset;
+    if (g_opt_raster.load(std::memory_order_relaxed) > 0) gp.raster_group = uint32_t(g_opt_raster.load());
     gp.raster_along_m = p.swizzleDirection;
     gp.idesc = make_idesc(128 * cta, p.n1, p.dtype == ACL_BF16 ? 1u : 0u, 0, p.layoutTagB == 1 ? 0u : 1u);
     gp.b_stage_bytes = (p.n1 / cta) * 128;
@@ -747,7 +749,7 @@ static int launch_fp8(Fp8Launch& L, void* workspace, cudaStream_t stream) {
         gp.k_blocks = kb_total;
         gp.num_m_blocks = ceil_div(L.m, 128 * L.mx_cta);
         gp.num_n_blocks = n_tiles;
-        gp.raster_group = 8;
+        gp.raster_group = g_opt_raster.load(std::memory_order_relaxed) > 0 ? uint32_t(g_opt_raster.load()) : 8u;
         gp.raster_along_m = L.m > L.n ? 0 : 1;
         // block-scaled instruction descriptor: e4m3 x e4m3, UE8M0 scales (bit 23), N >> 3 at [17,23), M >> 4 at [24,29)
         gp.idesc = (1u << 23) | ((L.mx_bn >> 3) << 17) | (((128u * L.mx_cta) >> 4) << 24);
@@ -1409,6 +1411,7 @@ aclnnStatus dgaSetOption(const char* name, int64_t value) {
     if (std::strcmp(name, "splitk_prefetch_kb") == 0) g_opt_splitk_prefetch.store(value);
     else if (std::strcmp(name, "pdl") == 0) g_opt_pdl.store(value);
     else if (std::strcmp(name, "splitk_issue_batch") == 0) g_opt_splitk_batch.store(value);
+    else if (std::strcmp(name, "raster_group") == 0) g_opt_raster.store(value);
     else {
         set_error(std::string("unknown option ") + name);
         return ACLNN_ERR_PARAM_INVALID;

@@ -140,6 +140,12 @@ def test_selector_decision_structure(dga):
     tiles = -(-4096 // 256) * -(-7168 // p["n1"])
     waves = -(-tiles // 74)
     assert tiles / (waves * 74) > 0.95, "wave quantisation: BalanceWorkload's job (utils.cpp:28-40)"
+    # under-filled and long K -> multicore split-K + reduce (the reference's declared kernel type 3 + StreamkReduceAdd)
+    p = dga.select_kernel(256, 4096, 7168)
+    assert p["kernelSerial"] == 5 and p["ctaGroup"] == 2 and p["n1"] == 256 and p["splitkFactor"] == 4
+    assert p["workspaceBytes"] == 4 * 256 * 4096 * 4 and p["blockDim"] == 128
+    assert dga.select_kernel(512, 4096, 7168)["kernelSerial"] in (0, 1)      # enough tiles: single pass
+    assert dga.select_kernel(256, 4096, 512)["kernelSerial"] in (0, 1)       # short K: nothing to split
     # at most one tile per cluster -> Small (select_kernel.cpp:285-289)
     assert dga.select_kernel(128, 128, 128)["kernelSerial"] in (1, 3)
 
