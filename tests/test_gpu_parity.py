@@ -355,3 +355,40 @@ def test_m_grouped_matmul_deepseek_shape(dga):
     for r in rows:
         ref = orc.golden_fp64(a[r:r + 1].float().cpu().numpy(), w[r // per].float().cpu().numpy().T)
         assert orc.max_rel_err(out[r:r + 1].float().cpu().numpy(), ref) <= 2.0 ** -7
+
+
+# ---- seeded fuzz over shapes, layouts, dtypes and plans (edge cases: tiny, ragged, odd pitches) ------------------------
+def _fuzz_cases(count=48, seed=20261104):
+    rng = np.random.RandomState(seed)
+    cases = []
+    for _ in range(count):
+        m = int(rng.choice([1, 2, 7, 16, 17, 63, 64, 100, 128, 129, 255, 256, 300, 513, 640]))
+        n = int(rng.choice([1, 8, 24, 64, 100, 128, 136, 250, 256, 384, 520, 777, 1024]))
+        k = int(rng.choice([1, 8, 16, 40, 64, 72, 128, 200, 256, 520, 1000, 1992]))
+        dtype = torch.bfloat16 if rng.rand() < 0.6 else torch.float16
+        layout_b = int(rng.rand() < 0.7)
+        kind = rng.randint(0, 6)
+        plan = {}
+        if kind == 1:
+            plan = {"kernelSerial": 0, "ctaGroup": int(rng.choice([1, 2])), "n1": int(rng.choice([64, 128, 192, 256]))}
+        elif kind == 2:
+            plan = {"kernelSerial": 4, "ctaGroup": int(rng.choice([1, 2])), "n1": int(rng.choice([64, 128, 256]))}
+        elif kind == 3 and k >= 128:
+            plan = {"kernelSerial": 5, "ctaGroup": int(rng.choice([1, 2])), "n1": int(rng.choice([64, 128, 256])),
+                    "splitkFactor": 2}
+        elif kind == 4 and m <= 256 and layout_b == 1 and k >= 256:
+            plan = {"kernelSerial": 3, "splitkFactor": int(rng.choice([1, 2, 4]))}
+        if (layout_b == 0 or k == 1) and plan.get("ctaGroup") == 2 and plan.get("n1") in (64, 192):
+            plan["n1"] = 128   # row-major B wants 64-column boxes per CTA (a [1,N] mat2 reads as row-major too)
+        cases.append((m, n, k, dtype, layout_b, plan))
+    return cases
+
+
+@pytest.mark.parametrize("m,n,k,dtype,layout_b,plan", _fuzz_cases())
+def test_fuzz_against_fp64_oracle(dga, m, n, k, dtype, layout_b, plan):
+    if dtype == torch.float16 and k > 1000:
+        dtype = torch.bfloat16
+    a, b = _inputs(m, n, k, dtype, seed=3 * m + 5 * n + 7 * k)
+    got = _run_aclnn(dga, a, b, dtype, layout_b, **plan)
+    err = orc.max_rel_err(got, orc.golden_fp64(a, b))
+    assert err <= (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7), "max rel err %.3e" % err
