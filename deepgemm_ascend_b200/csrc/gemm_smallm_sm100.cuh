@@ -195,19 +195,27 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
         const bool n_ok = n0 + row < p.n;
         // tmem_full fired: every MMA, hence every read of the ring, has completed; the ring is the staging tile now
         float* stage_out = reinterpret_cast<float*>(smem);
-        for (uint32_t c = 0; c < p.m; c += 16) {   // columns beyond m are padding: never read
-            uint32_t v[16];
-            ptx::tmem_ld_32x16(taddr + c, v);
+        // up to 64 activation columns per round: the TMEM loads go out back to back and share one wait
+        // (columns beyond m are padding: loaded at most up to the allocation, never used)
+        for (uint32_t c = 0; c < p.m; c += 64) {
+            uint32_t v[64];
+            const uint32_t left = p.m - c;
+            if (left <= 16) {
+                ptx::tmem_ld_32x16(taddr + c, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
+            } else {
+                ptx::tmem_ld_32x32(taddr + c, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+                if (left > 32) ptx::tmem_ld_32x32(taddr + c + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+            }
             ptx::tmem_ld_wait();
             if (split == 1) {
 #pragma unroll
-                for (uint32_t j = 0; j < 16; ++j)
-                    if (n_ok && c + j < p.m)
+                for (uint32_t j = 0; j < 64; ++j)
+                    if (n_ok && j < left)
                         store_out<OutT>(out + static_cast<uint64_t>(c + j) * p.ldc + n0 + row, __uint_as_float(v[j]));
             } else {
 #pragma unroll
-                for (uint32_t j = 0; j < 16; ++j)
-                    if (c + j < p.m) stage_out[(c + j) * 128 + row] = __uint_as_float(v[j]);
+                for (uint32_t j = 0; j < 64; ++j)
+                    if (j < left) stage_out[(c + j) * 128 + row] = __uint_as_float(v[j]);
             }
         }
         ptx::tc_fence_before();
