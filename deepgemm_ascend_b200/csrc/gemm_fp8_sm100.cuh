@@ -258,10 +258,12 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
                         const float s = sa_c * (which == 0 ? b0_c : which == 1 ? b1_c : b2_c);
                         if (ci & 1) {
 #pragma unroll
-                            for (uint32_t j = 0; j < 32; ++j) acc[ci][j] = fmaf(__uint_as_float(vb[j]), s, acc[ci][j]);
+                            for (uint32_t j = 0; j < 32; j += 2)
+                                ptx::fma2(acc[ci][j], acc[ci][j + 1], __uint_as_float(vb[j]), __uint_as_float(vb[j + 1]), s);
                         } else {
 #pragma unroll
-                            for (uint32_t j = 0; j < 32; ++j) acc[ci][j] = fmaf(__uint_as_float(va[j]), s, acc[ci][j]);
+                            for (uint32_t j = 0; j < 32; j += 2)
+                                ptx::fma2(acc[ci][j], acc[ci][j + 1], __uint_as_float(va[j]), __uint_as_float(va[j + 1]), s);
                         }
                     }
                 }

@@ -46,6 +46,19 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+// Packed fp32 FMA (FFMA2 on sm_100): {d0, d1} += {a0, a1} * s.  Two lanes per issue slot.
+__device__ __forceinline__ void fma2(float& d0, float& d1, float a0, float a1, float s) {
+    asm("{\n\t"
+        ".reg .b64 ra, rb, rc;\n\t"
+        "mov.b64 ra, {%2, %3};\n\t"
+        "mov.b64 rb, {%4, %4};\n\t"
+        "mov.b64 rc, {%0, %1};\n\t"
+        "fma.rn.f32x2 rc, ra, rb, rc;\n\t"
+        "mov.b64 {%0, %1}, rc;\n\t"
+        "}\n"
+        : "+f"(d0), "+f"(d1) : "f"(a0), "f"(a1), "f"(s));
+}
+
 __device__ __forceinline__ unsigned long long globaltimer() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
