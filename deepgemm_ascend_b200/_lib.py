@@ -83,6 +83,9 @@ SIGNATURES = {
     "dgaMGroupedMatmul": (_i32, [_vp, _u64, _vp, _vp]),
     "dgaSetOption": (_i32, [ctypes.c_char_p, ctypes.c_int64]),
     "dgaDebugReadTrace": (_i32, [_P(_u64), _u32]),
+    "dgaJitPrepare": (_i32, [_u32, _u32, _u32, _u32, _i32, _i32, _i32, ctypes.c_char_p, _u64]),
+    "dgaJitGetStats": (_i32, [_P(_u64), _P(_u64), _P(_u64)]),
+    "dgaJitDropMemoryCache": (_i32, []),
     "dgaGetLastError": (ctypes.c_char_p, []),
     "dgaKernelLaunchCount": (_u64, []),
     "dgaVersion": (ctypes.c_char_p, []),

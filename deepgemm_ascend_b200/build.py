@@ -16,8 +16,8 @@ LIB_DIR = os.path.join(PKG_DIR, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libdga_b200.so")
 STAMP = os.path.join(LIB_DIR, "libdga_b200.stamp")
 
-SOURCES = ["api.cu", "tile_selector.cpp", "plan_cache.cpp"]
-HEADERS = ["ptx.cuh", "gemm_sm100.cuh", "gemm_smallm_sm100.cuh", "gemm_fp8_sm100.cuh", "repack_sm100.cuh", "splitk_reduce_sm100.cuh", "tile_selector.h",
+SOURCES = ["api.cu", "tile_selector.cpp", "plan_cache.cpp", "jit.cpp"]
+HEADERS = ["ptx.cuh", "gemm_sm100.cuh", "gemm_smallm_sm100.cuh", "gemm_fp8_sm100.cuh", "repack_sm100.cuh", "splitk_reduce_sm100.cuh", "tile_selector.h", "jit.h", "jit_entry.cuh",
            os.path.join("..", "..", "include", "dga_b200.h")]
 
 NVCC_FLAGS = [

@@ -22,6 +22,7 @@
 #include "repack_sm100.cuh"
 #include "splitk_reduce_sm100.cuh"
 #include "tile_selector.h"
+#include "jit.h"
 
 namespace dga {
 
@@ -31,6 +32,12 @@ static std::atomic<int64_t> g_opt_splitk_prefetch{-1};
 static std::atomic<int64_t> g_opt_pdl{-1};
 static std::atomic<int64_t> g_opt_splitk_batch{-1};
 static std::atomic<int64_t> g_opt_raster{-1};   // raster_group override (sweeps)
+static std::atomic<int64_t> g_opt_jit{-1};      // shape-specialised kernels compiled at run time (default: $DGA_JIT)
+static bool jit_enabled() {
+    static const bool env = [] { const char* e = std::getenv("DGA_JIT"); return e != nullptr && std::atoi(e) != 0; }();
+    const int64_t opt = g_opt_jit.load(std::memory_order_relaxed);
+    return opt >= 0 ? opt != 0 : env;
+}
 
 #define DGA_CUDA(expr)                                                                       \
     do {                                                                                     \
@@ -193,9 +200,71 @@ static int set_smem_attr(K kernel, uint32_t bytes) {
     return ACLNN_SUCCESS;
 }
 
-template <int kCta, typename OutT, bool kBMn, int kMode = kModePlain>
+// The shape-derived constants of one launch as the JIT layer wants them (jit.h).
+static jit::Request make_jit_request(const DgaTilingPlan& p, int mode, uint32_t batch, const GemmParams& gp) {
+    jit::Request r;
+    r.batch = mode == kModeBatched ? batch : 1;
+    r.m = gp.m; r.n = gp.n; r.k = gp.k;
+    r.cta = p.ctaGroup;
+    r.in_dtype = p.dtype;
+    r.out_dtype = p.outDtype;
+    r.b_mn = p.layoutTagB != 1;
+    r.mode = mode;
+    r.block_n = gp.block_n; r.stages = gp.num_stages; r.k_blocks = gp.k_blocks;
+    r.m_blocks = gp.num_m_blocks; r.n_blocks = gp.num_n_blocks;
+    r.raster_group = gp.raster_group; r.raster_along_m = gp.raster_along_m;
+    r.idesc = gp.idesc; r.b_stage_bytes = gp.b_stage_bytes; r.k_block_elems = gp.k_block_elems;
+    r.dp_tiles = gp.dp_tiles; r.epi_cols = gp.epi_cols; r.tiles_per_batch = gp.tiles_per_batch;
+    return r;
+}
+
+// Launch through a kernel specialised for this exact shape and plan, compiled on first use (jit.cpp).  A compile
+// or load failure is an error of the call: there is no quiet return to the dynamic-shape kernel.
+static int launch_jit(const DenseLaunch& L, const GemmParams& gp, cudaStream_t stream, int mode) {
+    const jit::Request req = make_jit_request(L.plan, mode, L.batch, gp);
+    cudaKernel_t kernel = nullptr;
+    std::string err;
+    if (!jit::get_kernel(req, &kernel, &err)) {
+        set_error(err);
+        return ACLNN_ERR_RUNTIME_ERROR;
+    }
+    {
+        static std::mutex mu;
+        static std::map<cudaKernel_t, uint32_t> granted;
+        std::lock_guard<std::mutex> lock(mu);
+        uint32_t& have = granted[kernel];
+        if (L.plan.smemBytes > have) {
+            DGA_CUDA(cudaFuncSetAttribute(reinterpret_cast<const void*>(kernel),
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, int(L.plan.smemBytes)));
+            have = L.plan.smemBytes;
+        }
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(L.plan.blockDim);
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.dynamicSmemBytes = L.plan.smemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    fill_launch_attrs(cfg, attr, L.plan.ctaGroup);
+    void* args[] = {const_cast<CUtensorMap*>(&L.tm_a), const_cast<CUtensorMap*>(&L.tm_b),
+                    const_cast<CUtensorMap*>(&L.tm_d), const_cast<CUtensorMap*>(&L.tm_a),
+                    const_cast<CUtensorMap*>(&L.tm_b), const_cast<PeerMaps*>(&L.peers),
+                    const_cast<GemmParams*>(&gp)};
+    DGA_CUDA(cudaLaunchKernelExC(&cfg, reinterpret_cast<const void*>(kernel), args));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return ACLNN_SUCCESS;
+}
+
+template <int kCta, typename OutT, bool kBMn, int kMode = kModePlain, bool kSk = false>
 static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaStream_t stream) {
-    auto kernel = gemm_sm100_kernel<kCta, OutT, kBMn, false, kMode>;
+    if constexpr (kMode == kModePlain && !kSk) {
+        // a stream-K plan whose remainder came out empty is the plain walk
+        if (gp.sk_tiles != 0) return launch_common_inst<kCta, OutT, kBMn, kMode, true>(L, gp, stream);
+    }
+    if constexpr ((kMode == kModePlain || kMode == kModeBatched) && !kSk) {
+        if (jit_enabled() && L.num_peers == 0) return launch_jit(L, gp, stream, kMode);
+    }
+    auto kernel = gemm_sm100_kernel<kCta, OutT, kBMn, false, kMode, kSk>;
     int rc = set_smem_attr(kernel, L.plan.smemBytes);
     if (rc != ACLNN_SUCCESS) return rc;
     cudaLaunchConfig_t cfg{};
@@ -294,6 +363,26 @@ static int launch_splitk_reduce(const DenseLaunch& L, cudaStream_t stream) {
     return ACLNN_SUCCESS;
 }
 
+// The part of GemmParams that follows from the plan alone (whole tiles, one per work item).
+static void common_params(const DgaTilingPlan& p, GemmParams& gp) {
+    const uint32_t cta = p.ctaGroup;
+    gp.m = p.m; gp.n = p.n; gp.k = p.k;
+    gp.block_n = p.n1;
+    gp.num_stages = p.stages;
+    gp.k_blocks = ceil_div(p.k, 64);
+    gp.num_m_blocks = ceil_div(p.m, 128 * cta);
+    gp.num_n_blocks = ceil_div(p.n, p.n1);
+    gp.raster_group = p.swizzleOffset;
+    if (g_opt_raster.load(std::memory_order_relaxed) > 0) gp.raster_group = uint32_t(g_opt_raster.load());
+    gp.raster_along_m = p.swizzleDirection;
+    gp.idesc = make_idesc(128 * cta, p.n1, p.dtype == ACL_BF16 ? 1u : 0u, 0, p.layoutTagB == 1 ? 0u : 1u);
+    gp.b_stage_bytes = (p.n1 / cta) * 128;
+    gp.k_block_elems = 64;
+    gp.epi_cols = epi_cols_for(p.n1, elem_bytes(p.outDtype));
+    gp.dp_tiles = gp.num_m_blocks * gp.num_n_blocks;
+    gp.sk_tiles = 0;
+}
+
 static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     const DgaTilingPlan& p = L.plan;
     if (p.kernelSerial == DGA_KERNEL_SPLITK_REDUCE) {
@@ -313,22 +402,8 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     }
     const uint32_t cta = p.ctaGroup;
     GemmParams gp{};
-    gp.m = p.m; gp.n = p.n; gp.k = p.k;
-    gp.block_n = p.n1;
-    gp.num_stages = p.stages;
-    gp.k_blocks = ceil_div(p.k, 64);
-    gp.num_m_blocks = ceil_div(p.m, 128 * cta);
-    gp.num_n_blocks = ceil_div(p.n, p.n1);
-    gp.raster_group = p.swizzleOffset;
-    if (g_opt_raster.load(std::memory_order_relaxed) > 0) gp.raster_group = uint32_t(g_opt_raster.load());
-    gp.raster_along_m = p.swizzleDirection;
-    gp.idesc = make_idesc(128 * cta, p.n1, p.dtype == ACL_BF16 ? 1u : 0u, 0, p.layoutTagB == 1 ? 0u : 1u);
-    gp.b_stage_bytes = (p.n1 / cta) * 128;
-    gp.k_block_elems = 64;
+    common_params(p, gp);
     gp.num_peers = L.num_peers;
-    gp.epi_cols = epi_cols_for(p.n1, elem_bytes(p.outDtype));
-    gp.dp_tiles = gp.num_m_blocks * gp.num_n_blocks;
-    gp.sk_tiles = 0;
     if (p.kernelSerial == DGA_KERNEL_STREAMK) {
         const uint32_t clusters = p.blockDim / cta;
         streamk_split(gp.num_m_blocks * gp.num_n_blocks, clusters, gp.k_blocks, gp.dp_tiles, gp.sk_tiles);
@@ -1293,14 +1368,18 @@ static int plan_single_cta(DgaTilingPlan& p, uint32_t slabs_of_tiles) {
     return ACLNN_SUCCESS;
 }
 
+static int plan_batched(DgaTilingPlan& p, uint32_t batch, uint32_t m, uint32_t n, uint32_t k) {
+    seed_plan(p, m, n, k, ACL_BF16, ACL_FLOAT, /*layoutTagB=*/0);
+    p.strideA = k; p.strideB = n; p.strideC = n;
+    return plan_single_cta(p, batch);
+}
+
 // The framework kernel's batch loop (generate_code.hpp:149-153) as ONE launch: z[b] = x[b] * y[b], bf16 -> fp32,
 // row-major, 16-byte aligned pitches (k % 8 == 0, n % 8 == 0).
 static aclnnStatus framework_gemm_batched(const void* x, const void* y, void* z, uint32_t batch, uint32_t m, uint32_t n,
                                           uint32_t k, cudaStream_t stream) {
     DenseLaunch L;
-    seed_plan(L.plan, m, n, k, ACL_BF16, ACL_FLOAT, /*layoutTagB=*/0);
-    L.plan.strideA = k; L.plan.strideB = n; L.plan.strideC = n;
-    int rc = plan_single_cta(L.plan, batch);
+    int rc = plan_batched(L.plan, batch, m, n, k);
     if (rc != ACLNN_SUCCESS) return rc;
     L.mode = kModeBatched;
     L.batch = batch;
@@ -1412,10 +1491,65 @@ aclnnStatus dgaSetOption(const char* name, int64_t value) {
     else if (std::strcmp(name, "pdl") == 0) g_opt_pdl.store(value);
     else if (std::strcmp(name, "splitk_issue_batch") == 0) g_opt_splitk_batch.store(value);
     else if (std::strcmp(name, "raster_group") == 0) g_opt_raster.store(value);
+    else if (std::strcmp(name, "jit") == 0) g_opt_jit.store(value);
     else {
         set_error(std::string("unknown option ") + name);
         return ACLNN_ERR_PARAM_INVALID;
     }
+    return ACLNN_SUCCESS;
+}
+// ---- run-time specialisation (role of the framework's JIT layer, see jit.cpp) ---------------------------
+aclnnStatus dgaJitPrepare(uint32_t batch, uint32_t m, uint32_t n, uint32_t k, int32_t dtype, int32_t outDtype,
+                          int32_t layoutTagB, char* kernelDir, uint64_t kernelDirCapacity) {
+    DgaTilingPlan plan;
+    int mode = kModePlain;
+    aclnnStatus rc;
+    if (batch > 1) {
+        if (dtype != ACL_BF16 || outDtype != ACL_FLOAT || layoutTagB != 0) {
+            set_error("batched launches are built for bf16 x bf16 -> fp32 over row-major B (run_mmad_rtc)");
+            return ACLNN_ERR_PARAM_INVALID;
+        }
+        rc = plan_batched(plan, batch, m, n, k);
+        mode = kModeBatched;
+    } else {
+        seed_plan(plan, m, n, k, dtype, outDtype, layoutTagB);
+        rc = select_kernel_with_cache(plan);
+        if (rc == ACLNN_SUCCESS && plan.kernelSerial == DGA_KERNEL_STREAMK) plan.kernelSerial = DGA_KERNEL_COMMON;
+    }
+    if (rc != ACLNN_SUCCESS) return rc;
+    if (plan.kernelSerial != DGA_KERNEL_COMMON && plan.kernelSerial != DGA_KERNEL_PADDING_COMMON &&
+        plan.kernelSerial != DGA_KERNEL_SMALL) {
+        set_error("the plan for this shape uses a variant that is not specialised at run time (kernelSerial " +
+                  std::to_string(int(plan.kernelSerial)) + ")");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    GemmParams gp{};
+    common_params(plan, gp);
+    if (mode == kModeBatched) {
+        gp.tiles_per_batch = gp.dp_tiles;
+        gp.dp_tiles *= batch;
+    }
+    const jit::Request req = make_jit_request(plan, mode, batch, gp);
+    std::string dir, err;
+    if (!jit::ensure_compiled(req, &dir, &err)) {
+        set_error(err);
+        return ACLNN_ERR_RUNTIME_ERROR;
+    }
+    if (kernelDir != nullptr && kernelDirCapacity != 0) {
+        std::strncpy(kernelDir, dir.c_str(), kernelDirCapacity - 1);
+        kernelDir[kernelDirCapacity - 1] = '\0';
+    }
+    return ACLNN_SUCCESS;
+}
+aclnnStatus dgaJitGetStats(uint64_t* compiled, uint64_t* diskHits, uint64_t* memoryHits) {
+    const jit::Stats st = jit::stats();
+    if (compiled != nullptr) *compiled = st.compiled;
+    if (diskHits != nullptr) *diskHits = st.disk_hits;
+    if (memoryHits != nullptr) *memoryHits = st.memory_hits;
+    return ACLNN_SUCCESS;
+}
+aclnnStatus dgaJitDropMemoryCache(void) {
+    jit::drop_memory_cache();
     return ACLNN_SUCCESS;
 }
 aclnnStatus dgaDebugReadTrace(uint64_t* out, uint32_t words) {

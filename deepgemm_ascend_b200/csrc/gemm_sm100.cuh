@@ -80,15 +80,22 @@ struct PeerMaps {
 struct WorkItem {
     uint32_t tile, kb0, kb1;
 };
+// kSk = false (every variant except stream-K): whole tiles only; the 64-bit unit arithmetic and, in the epilogue,
+// the whole partial-tile path drop out of the kernel (measured: 1.2 us of a 30 us launch at M=512, 0.9 of 8.6 us at
+// 1024^3, profiles/r01_jit_keep_rt.log).
+template <bool kSk>
 struct WorkIter {
     uint32_t clusters, cid, dp_tiles, kb_total;
     uint32_t next_dp;
     uint64_t u, u_end;       // stream-K units (tile-local index * kb_total + kb) still to do
     __device__ __forceinline__ WorkIter(const GemmParams& p, uint32_t cluster_id, uint32_t num_clusters)
-        : clusters(num_clusters), cid(cluster_id), dp_tiles(p.dp_tiles), kb_total(p.k_blocks), next_dp(cluster_id) {
-        const uint64_t total = static_cast<uint64_t>(p.sk_tiles) * p.k_blocks;
-        u = begin_of(total, cluster_id, num_clusters);
-        u_end = begin_of(total, cluster_id + 1, num_clusters);
+        : clusters(num_clusters), cid(cluster_id), dp_tiles(p.dp_tiles), kb_total(p.k_blocks), next_dp(cluster_id),
+          u(0), u_end(0) {
+        if constexpr (kSk) {
+            const uint64_t total = static_cast<uint64_t>(p.sk_tiles) * p.k_blocks;
+            u = begin_of(total, cluster_id, num_clusters);
+            u_end = begin_of(total, cluster_id + 1, num_clusters);
+        }
     }
     static __device__ __forceinline__ uint64_t begin_of(uint64_t total, uint32_t c, uint32_t clusters) {
         return total * c / clusters;
@@ -99,13 +106,17 @@ struct WorkIter {
             next_dp += clusters;
             return true;
         }
-        if (u >= u_end) return false;
-        const uint32_t local = static_cast<uint32_t>(u / kb_total);
-        w.tile = dp_tiles + local;
-        w.kb0 = static_cast<uint32_t>(u - static_cast<uint64_t>(local) * kb_total);
-        w.kb1 = static_cast<uint32_t>(min(static_cast<uint64_t>(kb_total), w.kb0 + (u_end - u)));
-        u += w.kb1 - w.kb0;
-        return true;
+        if constexpr (!kSk) {
+            return false;
+        } else {
+            if (u >= u_end) return false;
+            const uint32_t local = static_cast<uint32_t>(u / kb_total);
+            w.tile = dp_tiles + local;
+            w.kb0 = static_cast<uint32_t>(u - static_cast<uint64_t>(local) * kb_total);
+            w.kb1 = static_cast<uint32_t>(min(static_cast<uint64_t>(kb_total), w.kb0 + (u_end - u)));
+            u += w.kb1 - w.kb0;
+            return true;
+        }
     }
 };
 
@@ -249,16 +260,19 @@ __device__ __forceinline__ void resolve_item(const GemmParams& p, WorkItem& w, u
         slab = 0;
     }
 }
-template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain>
-__global__ void __launch_bounds__(kNumThreads, 1)
-gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
-                  const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_sfa,
-                  const __grid_constant__ CUtensorMap tm_sfb, const __grid_constant__ PeerMaps peers,
-                  const GemmParams p) {
+// The kernel body is a device function so that two entries can share it: the dynamic-shape kernel below (every
+// field of GemmParams read at run time) and the shape-specialised entry a JIT build wraps around it
+// (jit_entry.cuh: the shape fields are compile-time constants there and fold through the inlined body).
+// The tensor maps must be the kernel's own __grid_constant__ parameters (TMA takes their address).
+template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain, bool kSk = false>
+__device__ __forceinline__ void
+gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensorMap& tm_d, const CUtensorMap& tm_sfa,
+                const CUtensorMap& tm_sfb, const PeerMaps& peers, const GemmParams& p) {
     static_assert(!(kMx && kBMn), "block-scaled fp8 wants K-major operands");
     static_assert(kMode == kModePlain || kMode == kModeSplitK || (kCta == 1 && !kMx),
                   "batched / grouped modes are single-CTA, 16-bit");
     static_assert(kMode != kModeSplitK || (sizeof(OutT) == 4 && !kMx), "split-K slices leave fp32 partial tiles");
+    static_assert(!kSk || (kMode == kModePlain && !kMx), "stream-K is a variant of the plain 16-bit kernel");
     ptx::grid_dep_launch();   // the next grid on the stream may set itself up while this one runs
     const bool tracing = (p.debug & 16) != 0 && p.trace != nullptr;
     if (tracing && threadIdx.x == 0) {
@@ -325,7 +339,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         // The whole warp walks the loop converged (uniform registers hold the addresses); one elected
         // lane issues.  A divergent `lane == 0` loop costs an ELECT/R2UR shuffle per operand.
         uint32_t stage = 0, phase = 0;
-        WorkIter it(p, cluster_id, num_clusters);
+        WorkIter<kSk> it(p, cluster_id, num_clusters);
         WorkItem w;
         while (it.next(w)) {
             uint32_t mb, nb, slab;
@@ -418,7 +432,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
             const uint32_t tmem_sfa = tmem_base + 2 * p.block_n;   // 4 columns; B scales follow
             const uint32_t tmem_sfb = tmem_sfa + 4;
             uint32_t stage = 0, phase = 0, iter = 0;
-            WorkIter it(p, cluster_id, num_clusters);
+            WorkIter<kSk> it(p, cluster_id, num_clusters);
             WorkItem w;
             for (; it.next(w); ++iter) {
                 uint32_t slab_unused;
@@ -507,7 +521,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
             }
             buf ^= 1;
         };
-        WorkIter it(p, cluster_id, num_clusters);
+        WorkIter<kSk> it(p, cluster_id, num_clusters);
         WorkItem w;
         for (; it.next(w); ++iter) {
             uint32_t mb, nb, slab;
@@ -532,7 +546,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                 if constexpr (kCta == 2) ptx::mbar_arrive_remote(&tmem_empty_bar[as], 0);
                 else ptx::mbar_arrive(&tmem_empty_bar[as]);
             };
-            if (kMode == kModeSplitK || w.kb1 - w.kb0 == p.k_blocks) {
+            if (kMode == kModeSplitK || !kSk || w.kb1 - w.kb0 == p.k_blocks) {
                 for (uint32_t c = 0; c < chunks; ++c) {
                     uint32_t v[32];
                     ptx::tmem_ld_32x32(taddr + c * kEpiCols, v);
@@ -548,7 +562,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
                 const uint64_t slot_floats = static_cast<uint64_t>(kBlockM) * p.block_n;
                 auto slot_of = [&](uint32_t cluster) {
                     // a cluster's slice of this tile is its head (it starts where the cluster's range starts) or its tail
-                    const uint32_t which = WorkIter::begin_of(total, cluster, num_clusters) >= u_tile ? 0u : 1u;
+                    const uint32_t which = WorkIter<kSk>::begin_of(total, cluster, num_clusters) >= u_tile ? 0u : 1u;
                     return p.sk_partials + ((static_cast<uint64_t>(cluster) * 2 + which) * kCta + cta_rank) * slot_floats;
                 };
                 // slot layout [chunk][4-column group][row] of 16-byte words: a warp's 32 rows are contiguous
@@ -623,6 +637,15 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         p.trace[blockIdx.x * 6 + 3] = ptx::globaltimer();
         p.trace[blockIdx.x * 6 + 5] = clock64();
     }
+}
+
+template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain, bool kSk = false>
+__global__ void __launch_bounds__(kNumThreads, 1)
+gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                  const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_sfa,
+                  const __grid_constant__ CUtensorMap tm_sfb, const __grid_constant__ PeerMaps peers,
+                  const GemmParams p) {
+    gemm_sm100_body<kCta, OutT, kBMn, kMx, kMode, kSk>(tm_a, tm_b, tm_d, tm_sfa, tm_sfb, peers, p);
 }
 
 }  // namespace dga

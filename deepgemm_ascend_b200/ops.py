@@ -147,6 +147,28 @@ def set_option(name, value):
     check(lib.dgaSetOption(name.encode(), int(value)), "dgaSetOption")
 
 
+def jit_prepare(m, n, k, dtype=_lib.ACL_BF16, out_dtype=None, layout_b=1, batch=1):
+    """Compile (or find in $DGA_ROOT_DIR) the kernel specialised for this shape ahead of its first use; needs nvcc
+    but no GPU. Returns the kernel directory (role of Compiler::build, framework/csrc/jit/compiler.hpp:26-52)."""
+    import ctypes
+    buf = ctypes.create_string_buffer(1024)
+    out_dtype = dtype if out_dtype is None else out_dtype
+    check(lib.dgaJitPrepare(batch, m, n, k, dtype, out_dtype, layout_b, buf, len(buf)), "dgaJitPrepare")
+    return buf.value.decode()
+
+
+def jit_stats():
+    """{'compiled': nvcc runs, 'disk_hits': kernel directories reused, 'memory_hits': in-process map hits}."""
+    import ctypes
+    vals = [ctypes.c_uint64() for _ in range(3)]
+    check(lib.dgaJitGetStats(*[ctypes.byref(v) for v in vals]), "dgaJitGetStats")
+    return dict(zip(("compiled", "disk_hits", "memory_hits"), (int(v.value) for v in vals)))
+
+
+def jit_drop_memory_cache():
+    check(lib.dgaJitDropMemoryCache(), "dgaJitDropMemoryCache")
+
+
 def kernel_launch_count():
     return int(lib.dgaKernelLaunchCount())
 
