@@ -174,6 +174,7 @@ def run_ours(args, rank, world):
             "config": {"workload": B.describe(args.workload, shape, world),
                        "l2_policy": "rotating %d buffer sets (%.0f MB > 2x L2)" % (sets, sets * nbytes / 1e6),
                        "launches_per_step": launches_per_step,
+                       "jit": os.environ.get("DGA_JIT", "0") not in ("", "0"),   # shape-specialised kernels
                        "plan": {key: plan.get(key) for key in ("kernelSerial", "ctaGroup", "m1", "n1", "k1", "stages",
                                                                "splitkFactor", "blockDim")}},
             "ms_per_step_median": per_step[len(per_step) // 2], "ms_per_step_min": per_step[0],

@@ -80,6 +80,7 @@ SIGNATURES = {
                                             ctypes.c_int64, _P(_u64), _P(_vp)]),
     "dgaNShardMatmul": (_i32, [_vp, _u64, _vp, _vp]),
     "dgaMGroupedMatmulGetWorkspaceSize": (_i32, [_P(AclTensor)] * 4 + [_P(_u64), _P(_vp)]),
+    "dgaMGroupedMaskedMatmulGetWorkspaceSize": (_i32, [_P(AclTensor)] * 4 + [_P(_u64), _P(_vp)]),
     "dgaMGroupedMatmul": (_i32, [_vp, _u64, _vp, _vp]),
     "dgaSetOption": (_i32, [ctypes.c_char_p, ctypes.c_int64]),
     "dgaDebugReadTrace": (_i32, [_P(_u64), _u32]),

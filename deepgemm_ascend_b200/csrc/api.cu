@@ -310,7 +310,7 @@ static int encode_common(DenseLaunch& L) {
         const CUtensorMapSwizzle d_swz3 = epi3 * elem_bytes(p.outDtype) == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
                                                                                 : CU_TENSOR_MAP_SWIZZLE_64B;
         int rc3;
-        if (L.mode == kModeBatched) {
+        if (mode_is_batched(L.mode)) {
             rc3 = make_tmap_3d(&L.tm_a, L.eff.a, p.dtype, p.k, p.m, L.batch, L.eff.lda, L.slab_a, 64, 128,
                                CU_TENSOR_MAP_SWIZZLE_128B);
             if (rc3 != ACLNN_SUCCESS) return rc3;
@@ -321,7 +321,7 @@ static int encode_common(DenseLaunch& L) {
             rc3 = make_tmap_2d(&L.tm_d, L.eff.d, p.outDtype, p.n, p.m, L.eff.ldd, epi3, 128, d_swz3);
         }
         if (rc3 != ACLNN_SUCCESS) return rc3;
-        const uint64_t slabs = L.mode == kModeBatched ? L.batch : L.groups;
+        const uint64_t slabs = mode_is_batched(L.mode) ? L.batch : L.groups;
         if (p.layoutTagB == 1)
             return make_tmap_3d(&L.tm_b, L.eff.b, p.dtype, p.k, p.n, slabs, L.eff.ldb, L.slab_b, 64, load_n,
                                 CU_TENSOR_MAP_SWIZZLE_128B);
@@ -453,7 +453,7 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
         // row-major B, and the MoE grouped GEMM over [G,N,K] weights with a 16-bit output
         gp.tiles_per_batch = gp.dp_tiles;
         gp.group_index = L.group_index;
-        if (L.mode == kModeBatched) gp.dp_tiles *= L.batch;
+        if (mode_is_batched(L.mode)) gp.dp_tiles *= L.batch;
         if (cta != 1 || p.kernelSerial == DGA_KERNEL_STREAMK) {
             set_error("batched / grouped launches use single-CTA whole tiles");
             return ACLNN_ERR_INNER_TILING_ERROR;
@@ -464,6 +464,10 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
             return launch_common_inst<1, __nv_bfloat16, false, kModeMGrouped>(L, gp, stream);
         if (L.mode == kModeMGrouped && p.layoutTagB == 1 && p.outDtype == ACL_FLOAT16)
             return launch_common_inst<1, __half, false, kModeMGrouped>(L, gp, stream);
+        if (L.mode == kModeMasked && p.layoutTagB == 1 && p.outDtype == ACL_BF16)
+            return launch_common_inst<1, __nv_bfloat16, false, kModeMasked>(L, gp, stream);
+        if (L.mode == kModeMasked && p.layoutTagB == 1 && p.outDtype == ACL_FLOAT16)
+            return launch_common_inst<1, __half, false, kModeMasked>(L, gp, stream);
         set_error("this dtype / layout combination is not built for batched / grouped launches");
         return ACLNN_ERR_PARAM_INVALID;
     }
@@ -1246,9 +1250,74 @@ aclnnStatus dgaMGroupedMatmulGetWorkspaceSize(const aclTensor* self, const aclTe
     *executor = ex;
     return ACLNN_SUCCESS;
 }
+// Masked layout: self [G, Mmax, K], weight [G, N, K], maskedM [G] int32, out [G, Mmax, N].
+aclnnStatus dgaMGroupedMaskedMatmulGetWorkspaceSize(const aclTensor* self, const aclTensor* weight,
+                                                    const aclTensor* maskedM, const aclTensor* out,
+                                                    uint64_t* workspaceSize, aclOpExecutor** executor) {
+    if (!self || !weight || !maskedM || !out || !workspaceSize || !executor) {
+        set_error("null argument");
+        return ACLNN_ERR_PARAM_NULLPTR;
+    }
+    if (self->ndim != 3 || weight->ndim != 3 || maskedM->ndim != 1 || out->ndim != 3) {
+        set_error("Invalid input dimensions. self [G,Mmax,K], weight [G,N,K], maskedM [G], out [G,Mmax,N]");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (self->dtype != weight->dtype || !dtype_ok_in(self->dtype) || out->dtype != self->dtype ||
+        maskedM->dtype != kAclInt32) {
+        set_error("self, weight and out must share a dtype in {float16, bfloat16}; maskedM must be int32");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    const int64_t g = self->shape[0], m = self->shape[1], k = self->shape[2], n = weight->shape[1];
+    if (weight->shape[2] != k) {
+        set_error("K dimension mismatch: self[2]=" + std::to_string(k) + " weight[2]=" + std::to_string(weight->shape[2]));
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (weight->shape[0] != g || maskedM->shape[0] != g || out->shape[0] != g || out->shape[1] != m || out->shape[2] != n) {
+        set_error("weight must be [G, N, K], maskedM [G] and out [G, Mmax, N]");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (m <= 0 || n <= 0 || k <= 0 || g <= 0 || m > UINT32_MAX || n > UINT32_MAX || k > UINT32_MAX || g > UINT32_MAX) {
+        set_error("g, m, n, k must be positive 32-bit values");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    if (self->stride[2] != 1 || weight->stride[2] != 1 || out->stride[2] != 1 || maskedM->stride[0] != 1 ||
+        self->stride[1] < k || weight->stride[1] < k || out->stride[1] < n ||
+        (g > 1 && (self->stride[0] < self->stride[1] * m || weight->stride[0] < weight->stride[1] * n ||
+                   out->stride[0] < out->stride[1] * m))) {
+        set_error("self, weight (K contiguous) and out must be row-major per group");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    aclOpExecutor* ex = new aclOpExecutor{};
+    DenseLaunch& L = ex->dense;
+    seed_plan(L.plan, uint32_t(m), uint32_t(n), uint32_t(k), self->dtype, out->dtype, /*layoutTagB=*/1);
+    L.a = self->data; L.b = weight->data; L.d = out->data;
+    L.lda = uint64_t(self->stride[1]); L.ldb = uint64_t(weight->stride[1]); L.ldd = uint64_t(out->stride[1]);
+    L.plan.strideA = L.lda; L.plan.strideB = L.ldb; L.plan.strideC = L.ldd;
+    L.mode = kModeMasked;
+    L.batch = uint32_t(g);
+    L.slab_a = g > 1 ? uint64_t(self->stride[0]) : uint64_t(m) * L.lda;
+    L.slab_b = g > 1 ? uint64_t(weight->stride[0]) : uint64_t(n) * L.ldb;
+    L.slab_d = g > 1 ? uint64_t(out->stride[0]) : uint64_t(m) * L.ldd;
+    L.group_index = static_cast<const int32_t*>(maskedM->data);
+    int rc = plan_single_cta(L.plan, uint32_t(g));
+    if (rc == ACLNN_SUCCESS &&
+        (((L.lda | L.ldb | L.ldd | L.slab_a | L.slab_b | L.slab_d) * 2) % 16 != 0 ||
+         ((reinterpret_cast<uintptr_t>(L.a) | reinterpret_cast<uintptr_t>(L.b) | reinterpret_cast<uintptr_t>(L.d)) & 15))) {
+        set_error("grouped matmul wants 16-byte aligned base pointers and pitches");
+        rc = ACLNN_ERR_INNER_TILING_ERROR;
+    }
+    if (rc != ACLNN_SUCCESS) {
+        delete ex;
+        return rc;
+    }
+    *workspaceSize = 0;
+    *executor = ex;
+    return ACLNN_SUCCESS;
+}
 aclnnStatus dgaMGroupedMatmul(void* workspace, uint64_t workspaceSize, aclOpExecutor* executor, aclrtStream stream) {
     (void)workspace; (void)workspaceSize;
-    if (executor == nullptr || executor->is_fp8 || executor->dense.mode != kModeMGrouped) {
+    if (executor == nullptr || executor->is_fp8 ||
+        (executor->dense.mode != kModeMGrouped && executor->dense.mode != kModeMasked)) {
         set_error("not a grouped-matmul executor");
         return ACLNN_ERR_PARAM_NULLPTR;
     }

@@ -59,6 +59,8 @@ struct GemmParams {
     unsigned long long* trace; // debug & 16: per CTA {t_start, t_first_data, t_last_mma_issued, t_end (ns), clk_start, clk_end}
     // kMode 1 (batched: A [B,M,K], B [B,K,N] or [B,N,K], D [B,M,N], 3-D tensor maps): tiles per batch entry
     // kMode 2 (M-grouped contiguous: A [M_total,K], B [G,N,K], D [M_total,N]): group of every row, -1 = skip
+    // kMode 4 (M-grouped masked: batched addressing over groups, group_index[g] = valid rows of group g; 128-row
+    //         blocks at or past it are skipped by every role and left unwritten)
     // kMode 3 (split-K: work item = K slice `i % split_k` of tile `i / split_k`; fp32 partial tiles go to slab
     //         [slice] of a [split_k, M, N] workspace behind a 3-D tensor map, splitk_reduce_kernel adds them up)
     uint32_t tiles_per_batch;
@@ -244,11 +246,13 @@ __host__ __device__ inline SmemLayout make_smem_layout(uint32_t d_stage_bytes, u
 // kMode 3: multicore split-K (the reference declares it as kernel type 3, catlass_dynamic_matmul_tiling_key.h:117-130,
 // and never dispatches it) for shapes whose tiles fill well under one wave: every tile's K range is cut into
 // split_k slices that run as independent work items; see splitk_reduce_sm100.cuh for the second half.
-constexpr int kModePlain = 0, kModeBatched = 1, kModeMGrouped = 2, kModeSplitK = 3;
+constexpr int kModePlain = 0, kModeBatched = 1, kModeMGrouped = 2, kModeSplitK = 3, kModeMasked = 4;
+// batched addressing (third tensor-map coordinate = tile / tiles_per_batch)
+constexpr bool mode_is_batched(int mode) { return mode == kModeBatched || mode == kModeMasked; }
 // Turns the iterator's item into (tile, K-block range, slab = third coordinate of the 3-D maps).
 template <int kMode>
 __device__ __forceinline__ void resolve_item(const GemmParams& p, WorkItem& w, uint32_t& slab) {
-    if constexpr (kMode == kModeBatched) {
+    if constexpr (mode_is_batched(kMode)) {
         slab = w.tile / p.tiles_per_batch;
         w.tile -= slab * p.tiles_per_batch;
     } else if constexpr (kMode == kModeSplitK) {
@@ -352,6 +356,9 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                 z = __ldg(p.group_index + m_idx);
                 if (z < 0) continue;   // every role skips the same blocks
             }
+            if constexpr (kMode == kModeMasked) {
+                if (m_idx >= __ldg(p.group_index + slab)) continue;
+            }
             for (uint32_t kb = w.kb0; kb < w.kb1; ++kb) {
                 ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                 if (p.debug & 1) {
@@ -393,7 +400,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                         if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * (L.a_stage_bytes + L.b_stage_bytes + sf_bytes));
                         else ptx::mbar_arrive_remote(&full_bar[stage], 0);
                     } else {
-                        if constexpr (kMode == kModeBatched) ptx::tma_load_3d(&tm_a, &full_bar[stage], sa, k_idx, m_idx, z);
+                        if constexpr (mode_is_batched(kMode)) ptx::tma_load_3d(&tm_a, &full_bar[stage], sa, k_idx, m_idx, z);
                         else ptx::tma_load_2d(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
                         if constexpr (kBMn) {
                             for (uint32_t j = 0; j < load_n / 64; ++j) {
@@ -435,12 +442,13 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             WorkIter<kSk> it(p, cluster_id, num_clusters);
             WorkItem w;
             for (; it.next(w); ++iter) {
-                uint32_t slab_unused;
-                resolve_item<kMode>(p, w, slab_unused);
-                if constexpr (kMode == kModeMGrouped) {
+                uint32_t slab_of_item;
+                resolve_item<kMode>(p, w, slab_of_item);
+                if constexpr (kMode == kModeMGrouped || kMode == kModeMasked) {
                     uint32_t mb, nb;
                     tile_coords(p, w.tile, mb, nb);
-                    if (__ldg(p.group_index + mb * kBlockM) < 0) { --iter; continue; }
+                    const int32_t g = __ldg(p.group_index + (kMode == kModeMasked ? slab_of_item : mb * kBlockM));
+                    if (kMode == kModeMasked ? static_cast<int32_t>(mb * kBlockM) >= g : g < 0) { --iter; continue; }
                 }
                 const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
                 ptx::mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
@@ -509,7 +517,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             if (epi_tid == 0) {
                 const int32_t c0 = static_cast<int32_t>(col - half * kEpiCols);
                 if (m0 < p.m && !(p.debug & 4)) {
-                    if constexpr (kMode == kModeBatched || kMode == kModeSplitK)
+                    if constexpr (mode_is_batched(kMode) || kMode == kModeSplitK)
                         ptx::tma_store_3d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes, c0, static_cast<int32_t>(m0), zb);
                     else
                         ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes, c0, static_cast<int32_t>(m0));
@@ -532,6 +540,9 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             const uint32_t n0 = nb * p.block_n;
             if constexpr (kMode == kModeMGrouped) {
                 if (__ldg(p.group_index + m0) < 0) { --iter; continue; }
+            }
+            if constexpr (kMode == kModeMasked) {
+                if (static_cast<int32_t>(m0) >= __ldg(p.group_index + slab)) { --iter; continue; }
             }
             const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
             // chunks that intersect the matrix (TMA clips a partial last one)

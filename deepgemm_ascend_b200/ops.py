@@ -196,6 +196,22 @@ def m_grouped_matmul(self, weight, group_index, out=None, stream=None):
     return out
 
 
+def m_grouped_matmul_masked(self, weight, masked_m, out=None, stream=None):
+    """out[g,i,:] = self[g,i,:] @ weight[g].T for i < masked_m[g]; self [G,Mmax,K], weight [G,N,K], masked_m int32 [G]
+    on the device (no host sync). Whole 128-row blocks past masked_m[g] are skipped and left unwritten."""
+    _require_cuda(self, weight, masked_m)
+    if out is None:
+        out = torch.empty((self.shape[0], self.shape[1], weight.shape[1]), dtype=self.dtype, device=self.device)
+    ws = ctypes.c_uint64(0)
+    ex = ctypes.c_void_p(None)
+    a, w, g, c = acl_tensor(self), acl_tensor(weight), acl_tensor(masked_m), acl_tensor(out)
+    check(lib.dgaMGroupedMaskedMatmulGetWorkspaceSize(ctypes.byref(a), ctypes.byref(w), ctypes.byref(g),
+                                                      ctypes.byref(c), ctypes.byref(ws), ctypes.byref(ex)),
+          "dgaMGroupedMaskedMatmulGetWorkspaceSize")
+    check(lib.dgaMGroupedMatmul(ctypes.c_void_p(None), 0, ex, _stream_ptr(stream)), "dgaMGroupedMatmul")
+    return out
+
+
 class MGroupedExecutor:
     """Repeatable grouped-matmul plan: phase 1 once, phase 2 per call."""
 

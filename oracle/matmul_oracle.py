@@ -217,6 +217,19 @@ def m_grouped_golden_fp64(a, w, group_index):
     return out
 
 
+def m_grouped_masked_golden_fp64(a, w, masked_m):
+    """M-grouped masked matmul (MoE decode): out[g,i,:] = a[g,i,:] . w[g]^T in fp64 for i < masked_m[g]; the other
+    rows come back as NaN (don't-care on the device).  Not in the reference; semantics of upstream
+    deepseek-ai/DeepGEMM `m_grouped_*_gemm_nt_masked` (a [G,Mmax,K], b [G,N,K], masked_m [G]); parity unpinned by the
+    reference, anchored on the fp64 rule of north_star."""
+    a64, w64 = a.astype(np.float64), w.astype(np.float64)
+    out = np.full((a.shape[0], a.shape[1], w.shape[1]), np.nan, dtype=np.float64)
+    for g in range(a.shape[0]):
+        rows = int(masked_m[g])
+        out[g, :rows] = a64[g, :rows] @ w64[g].T
+    return out
+
+
 def align16(x):
     return (x + 15) & ~15
 

@@ -82,6 +82,40 @@ def test_phase1_validation_matches_reference_rules(dga, capfd):
     assert rc == 0
 
 
+def test_grouped_phase1_validation(dga, capfd):
+    """Shape / dtype rules of the two MoE layouts (contiguous: self [M,K], weight [G,N,K], index [M]; masked: self
+    [G,Mmax,K], weight [G,N,K], maskedM [G]); phase 1 needs no GPU."""
+    BF16, I32 = 27, 3
+    L = dga._lib.lib
+
+    def phase1(fn, *tensors):
+        ws, ex = ctypes.c_uint64(0), ctypes.c_void_p(None)
+        rc = fn(*[ctypes.byref(t) for t in tensors], ctypes.byref(ws), ctypes.byref(ex))
+        if rc == 0:
+            assert ws.value == 0
+            L.dgaDestroyExecutor(ex)
+        return rc
+
+    a = _desc(dga, (256, 128), (128, 1), BF16)
+    w = _desc(dga, (4, 512, 128), (512 * 128, 128, 1), BF16)
+    idx = _desc(dga, (256,), (1,), I32)
+    c = _desc(dga, (256, 512), (512, 1), BF16)
+    assert phase1(L.dgaMGroupedMatmulGetWorkspaceSize, a, w, idx, c) == 0
+    assert phase1(L.dgaMGroupedMatmulGetWorkspaceSize, _desc(dga, (200, 128), (128, 1), BF16), w,
+                  _desc(dga, (200,), (1,), I32), _desc(dga, (200, 512), (512, 1), BF16)) != 0   # M_total % 128
+    assert phase1(L.dgaMGroupedMatmulGetWorkspaceSize, a, w, _desc(dga, (256,), (1,), BF16), c) != 0  # index dtype
+
+    am = _desc(dga, (4, 200, 128), (200 * 128, 128, 1), BF16)
+    mm = _desc(dga, (4,), (1,), I32)
+    cm = _desc(dga, (4, 200, 512), (200 * 512, 512, 1), BF16)
+    assert phase1(L.dgaMGroupedMaskedMatmulGetWorkspaceSize, am, w, mm, cm) == 0
+    assert phase1(L.dgaMGroupedMaskedMatmulGetWorkspaceSize, am, w, _desc(dga, (3,), (1,), I32), cm) != 0   # G mismatch
+    assert phase1(L.dgaMGroupedMaskedMatmulGetWorkspaceSize, am, _desc(dga, (4, 512, 96), (512 * 96, 96, 1), BF16),
+                  mm, cm) != 0                                                                      # K mismatch
+    assert phase1(L.dgaMGroupedMaskedMatmulGetWorkspaceSize, a, w, mm, cm) != 0                     # self not 3-D
+    assert "[DGA] [ERROR]" in capfd.readouterr().err
+
+
 SWEEP = [1, 16, 64, 128, 512, 2048, 8192]
 
 

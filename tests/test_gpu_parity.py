@@ -357,6 +357,32 @@ def test_m_grouped_matmul_deepseek_shape(dga):
         assert orc.max_rel_err(out[r:r + 1].float().cpu().numpy(), ref) <= 2.0 ** -7
 
 
+@pytest.mark.parametrize("groups,m_max,n,k,dtype", [(4, 256, 512, 256, torch.bfloat16),
+                                                      (6, 384, 1000, 520, torch.bfloat16),
+                                                      (3, 200, 384, 1024, torch.float16)])
+def test_m_grouped_masked_matches_oracle(dga, groups, m_max, n, k, dtype):
+    rng = np.random.RandomState(groups + m_max + n + k)
+    masked = rng.randint(0, m_max + 1, size=groups).astype(np.int32)
+    masked[0], masked[-1] = 0, m_max                    # an empty group and a full one
+    a = np.stack([_inputs(m_max, 8, k, dtype, seed=40 + g)[0] for g in range(groups)])       # [G, Mmax, K]
+    w = np.stack([_inputs(8, n, k, dtype, seed=50 + g)[1].T for g in range(groups)])         # [G, N, K]
+    ta, tw = _to_dev(a, dtype), _to_dev(w, dtype)
+    out = torch.full((groups, m_max, n), 768.0, dtype=dtype, device=DEV)
+    before = dga.kernel_launch_count()
+    dga.m_grouped_matmul_masked(ta, tw, torch.from_numpy(masked).to(DEV), out=out)
+    torch.cuda.synchronize()
+    assert dga.kernel_launch_count() - before == 1
+    got = out.float().cpu().numpy()
+    ref = orc.m_grouped_masked_golden_fp64(a, w, masked)
+    tol = 2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7
+    for g in range(groups):
+        rows = int(masked[g])
+        if rows:
+            assert orc.max_rel_err(got[g, :rows], ref[g, :rows]) <= tol
+        first_skipped = -(-rows // 128) * 128            # whole blocks past masked_m are left untouched
+        assert np.all(got[g, first_skipped:] == 768.0)
+
+
 # ---- seeded fuzz over shapes, layouts, dtypes and plans (edge cases: tiny, ragged, odd pitches) ------------------------
 def _fuzz_cases(count=48, seed=20261104):
     rng = np.random.RandomState(seed)
