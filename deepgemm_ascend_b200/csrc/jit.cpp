@@ -117,15 +117,21 @@ bool compile(const std::string& dir, const std::string& code, std::string* err) 
         *err = "cannot create " + dir;
         return false;
     }
+    const std::string pid = std::to_string(::getpid());
     {
-        std::ofstream f(dir + kCodeName, std::ios::binary | std::ios::trunc);
+        // source and binary both reach their final names by rename: a concurrent builder of the same directory
+        // never reads a half-written file
+        const std::string code_tmp = dir + kCodeName + ".tmp" + pid;
+        std::ofstream f(code_tmp, std::ios::binary | std::ios::trunc);
         f << code;
-        if (!f.good()) {
+        f.close();
+        if (!f.good() || ::rename(code_tmp.c_str(), (dir + kCodeName).c_str()) != 0) {
             *err = "cannot write " + dir + kCodeName;
+            ::unlink(code_tmp.c_str());
             return false;
         }
     }
-    const std::string tmp = dir + kBinName + ".tmp" + std::to_string(::getpid());
+    const std::string tmp = dir + kBinName + ".tmp" + pid;
     const std::string command = compiler_path() +
         " -gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -lineinfo --expt-relaxed-constexpr -cubin -I" +
         include_dir() + " -o " + tmp + " " + dir + kCodeName;

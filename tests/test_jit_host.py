@@ -66,3 +66,33 @@ def test_compiler_failure_is_an_error(jit_root, monkeypatch):
 def test_unspecialised_variant_is_refused(jit_root):
     with pytest.raises(dga.DgaError, match="not specialised"):
         dga.jit_prepare(16, 4096, 7168)   # decode kernel
+
+
+def _prepare_in_child(root, queue):
+    os.environ["DGA_ROOT_DIR"] = root
+    import deepgemm_ascend_b200 as child_dga
+    try:
+        queue.put(("ok", child_dga.jit_prepare(896, 512, 192)))
+    except Exception as e:   # noqa: BLE001 - reported to the parent
+        queue.put(("error", repr(e)))
+
+
+def test_two_processes_racing_for_one_directory(jit_root):
+    """The binary appears under its final name only by rename, so concurrent builders of one kernel both succeed and
+    leave a loadable directory (the reference's cache has no such guard)."""
+    import multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    queue = ctx.Queue()
+    procs = [ctx.Process(target=_prepare_in_child, args=(str(jit_root), queue)) for _ in range(2)]
+    for p in procs:
+        p.start()
+    results = [queue.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert [r[0] for r in results] == ["ok", "ok"], results
+    d = results[0][1]
+    assert results[1][1] == d
+    assert sorted(os.listdir(d)) == ["kernel.cu", "kernel.cubin"]   # no temporary files left behind
+    before = dga.jit_stats()["compiled"]
+    assert dga.jit_prepare(896, 512, 192) == d
+    assert dga.jit_stats()["compiled"] == before                     # the directory is valid for a third process
