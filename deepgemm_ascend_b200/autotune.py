@@ -43,7 +43,9 @@ def candidate_plans(m, n, k, layout_b=1):
             for stages in (0, 4):          # 0 = as deep as shared memory allows
                 out.append({"kernelSerial": KERNEL_COMMON, "ctaGroup": cta, "n1": n1, "stages": stages})
             if m > 128:
-                out.append({"kernelSerial": KERNEL_STREAMK, "ctaGroup": cta, "n1": n1, "stages": 0})
+                for split in (0, 2, 4):    # 0 = slice count chosen by streamk_split
+                    out.append({"kernelSerial": KERNEL_STREAMK, "ctaGroup": cta, "n1": n1, "stages": 0,
+                                "splitkFactor": split})
     if m <= 256 and layout_b == 1:
         for split in (1, 2, 4, 8):
             if -(-k // 64) < split:

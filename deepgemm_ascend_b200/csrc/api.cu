@@ -405,10 +405,13 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     common_params(p, gp);
     gp.num_peers = L.num_peers;
     if (p.kernelSerial == DGA_KERNEL_STREAMK) {
-        const uint32_t clusters = p.blockDim / cta;
-        streamk_split(gp.num_m_blocks * gp.num_n_blocks, clusters, gp.k_blocks, gp.dp_tiles, gp.sk_tiles);
+        const uint32_t clusters = platform().smCount / cta;
+        uint32_t split = 1;
+        streamk_split(gp.num_m_blocks * gp.num_n_blocks, clusters, gp.k_blocks, p.splitkFactor, gp.dp_tiles, gp.sk_tiles,
+                      split);
+        gp.split_k = split;
         if (gp.sk_tiles != 0) {
-            const uint64_t part = streamk_partial_bytes(clusters, cta, p.n1);
+            const uint64_t part = streamk_partial_bytes(gp.sk_tiles, split, cta, p.n1);
             gp.sk_partials = static_cast<float*>(workspace);
             gp.sk_sems = reinterpret_cast<int32_t*>(static_cast<char*>(workspace) + part);
             // The counters are left at zero by the kernel (the last slice of a tile resets its counter), so they

@@ -52,7 +52,8 @@ struct GemmParams {
     const int32_t* gate;     // device flag; the kernel runs only when *gate == gate_expect (nullptr: always)
     int32_t gate_expect;
     // stream-K (role of PaddingStreamkMatmulKernel): the first dp_tiles tiles are walked whole, one per cluster
-    // and wave; the K blocks of the remaining sk_tiles tiles are dealt out evenly to all clusters.
+    // and wave; each of the remaining sk_tiles tiles (the ragged last wave) is cut into split_k K slices with
+    // aligned boundaries, and the sk_tiles * split_k slices are dealt out round-robin (tile-major) to all clusters.
     uint32_t dp_tiles, sk_tiles;
     uint32_t num_peers;      // extra destinations of every output chunk (PeerMaps)
     uint32_t epi_cols;       // columns per TMA store: 32, or 64 for 16-bit outputs when block_n % 64 == 0 (128-byte rows)
@@ -66,7 +67,7 @@ struct GemmParams {
     uint32_t tiles_per_batch;
     uint32_t split_k;
     const int32_t* group_index;
-    float* sk_partials;      // [cluster][head/tail][cta rank][128][block_n] fp32
+    float* sk_partials;      // [slice item][cta rank][128][block_n] fp32
     int32_t* sk_sems;        // [sk tile][cta rank] arrival counters, zero on entry and on exit
 };
 
@@ -81,42 +82,38 @@ struct PeerMaps {
 // One unit of work of a cluster: K blocks [kb0, kb1) of `tile`.  Every warp role walks the same sequence.
 struct WorkItem {
     uint32_t tile, kb0, kb1;
+    uint32_t item;           // stream-K: index of this slice among all slices (its partial slot); unused otherwise
 };
-// kSk = false (every variant except stream-K): whole tiles only; the 64-bit unit arithmetic and, in the epilogue,
-// the whole partial-tile path drop out of the kernel (measured: 1.2 us of a 30 us launch at M=512, 0.9 of 8.6 us at
+// kSk = false (every variant except stream-K): whole tiles only; the slice arithmetic and, in the epilogue, the
+// whole partial-tile path drop out of the kernel (measured: 1.2 us of a 30 us launch at M=512, 0.9 of 8.6 us at
 // 1024^3, profiles/r01_jit_keep_rt.log).
+// Why aligned slices and not an even deal of K blocks: clusters that work on tiles of one row / column panel at the
+// same K offset share the panel through L2 in time; with an even deal every cluster sits at its own K offset, every
+// panel block is fetched once per tile, and the variant ran load-bound (profiles/r01_streamk_probe.log).
 template <bool kSk>
 struct WorkIter {
-    uint32_t clusters, cid, dp_tiles, kb_total;
+    uint32_t clusters, dp_tiles, kb_total;
     uint32_t next_dp;
-    uint64_t u, u_end;       // stream-K units (tile-local index * kb_total + kb) still to do
+    uint32_t next_sk, sk_items, split;
     __device__ __forceinline__ WorkIter(const GemmParams& p, uint32_t cluster_id, uint32_t num_clusters)
-        : clusters(num_clusters), cid(cluster_id), dp_tiles(p.dp_tiles), kb_total(p.k_blocks), next_dp(cluster_id),
-          u(0), u_end(0) {
-        if constexpr (kSk) {
-            const uint64_t total = static_cast<uint64_t>(p.sk_tiles) * p.k_blocks;
-            u = begin_of(total, cluster_id, num_clusters);
-            u_end = begin_of(total, cluster_id + 1, num_clusters);
-        }
-    }
-    static __device__ __forceinline__ uint64_t begin_of(uint64_t total, uint32_t c, uint32_t clusters) {
-        return total * c / clusters;
-    }
+        : clusters(num_clusters), dp_tiles(p.dp_tiles), kb_total(p.k_blocks), next_dp(cluster_id),
+          next_sk(cluster_id), sk_items(kSk ? p.sk_tiles * p.split_k : 0u), split(kSk ? p.split_k : 1u) {}
     __device__ __forceinline__ bool next(WorkItem& w) {
         if (next_dp < dp_tiles) {
-            w.tile = next_dp; w.kb0 = 0; w.kb1 = kb_total;
+            w.tile = next_dp; w.kb0 = 0; w.kb1 = kb_total; w.item = 0;
             next_dp += clusters;
             return true;
         }
         if constexpr (!kSk) {
             return false;
         } else {
-            if (u >= u_end) return false;
-            const uint32_t local = static_cast<uint32_t>(u / kb_total);
+            if (next_sk >= sk_items) return false;
+            const uint32_t local = next_sk / split, slice = next_sk - local * split;
             w.tile = dp_tiles + local;
-            w.kb0 = static_cast<uint32_t>(u - static_cast<uint64_t>(local) * kb_total);
-            w.kb1 = static_cast<uint32_t>(min(static_cast<uint64_t>(kb_total), w.kb0 + (u_end - u)));
-            u += w.kb1 - w.kb0;
+            w.kb0 = slice * kb_total / split;
+            w.kb1 = (slice + 1) * kb_total / split;
+            w.item = next_sk;
+            next_sk += clusters;
             return true;
         }
     }
@@ -567,17 +564,14 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                 }
             } else {
                 // ---- stream-K slice: fp32 partial -> workspace; the last slice of the tile to arrive adds them up
-                // in a fixed order (deterministic) and stores the tile.
-                const uint64_t total = static_cast<uint64_t>(p.sk_tiles) * p.k_blocks;
-                const uint64_t u_tile = static_cast<uint64_t>(w.tile - p.dp_tiles) * p.k_blocks;
+                // in slice order (deterministic) and stores the tile.
                 const uint64_t slot_floats = static_cast<uint64_t>(kBlockM) * p.block_n;
-                auto slot_of = [&](uint32_t cluster) {
-                    // a cluster's slice of this tile is its head (it starts where the cluster's range starts) or its tail
-                    const uint32_t which = WorkIter<kSk>::begin_of(total, cluster, num_clusters) >= u_tile ? 0u : 1u;
-                    return p.sk_partials + ((static_cast<uint64_t>(cluster) * 2 + which) * kCta + cta_rank) * slot_floats;
+                auto slot_of = [&](uint32_t item) {
+                    return p.sk_partials + (static_cast<uint64_t>(item) * kCta + cta_rank) * slot_floats;
                 };
+                const uint32_t first = (w.tile - p.dp_tiles) * p.split_k, last = first + p.split_k - 1;
                 // slot layout [chunk][4-column group][row] of 16-byte words: a warp's 32 rows are contiguous
-                uint4* mine = reinterpret_cast<uint4*>(slot_of(cluster_id)) + epi_tid;
+                uint4* mine = reinterpret_cast<uint4*>(slot_of(w.item)) + epi_tid;
                 for (uint32_t c = 0; c < chunks; ++c) {
                     uint32_t v[32];
                     ptx::tmem_ld_32x32(taddr + c * kEpiCols, v);
@@ -593,9 +587,6 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                 if (epi_tid == 0) *sk_bcast = static_cast<uint32_t>(atomicAdd(sem, 1));
                 ptx::named_bar_sync(1, 128);
                 const uint32_t arrived = *sk_bcast;
-                // clusters whose ranges touch this tile: owner(u) = ceil((u + 1) * clusters / total) - 1
-                const uint32_t first = static_cast<uint32_t>(((u_tile + 1) * num_clusters + total - 1) / total) - 1;
-                const uint32_t last = static_cast<uint32_t>(((u_tile + p.k_blocks) * num_clusters + total - 1) / total) - 1;
                 if (arrived == last - first && (p.debug & 8)) {
                     if (epi_tid == 0) *sem = 0;   // isolation: skip the reduction
                 } else if (arrived == last - first) {

@@ -157,20 +157,38 @@ bool aligned16(uint64_t elems, uint32_t bytes) { return (elems * bytes) % 16 == 
 
 }  // namespace
 
-void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t& dp, uint32_t& sk) {
-    const uint32_t full = tiles / clusters, rem = tiles % clusters;
-    dp = tiles;
-    sk = 0;
-    if (rem == 0) return;
-    // hand the ragged last wave plus (when there is one) a whole wave to stream-K, so that no slice is thin
-    const uint32_t sk_try = full >= 1 ? clusters + rem : tiles;
-    if (uint64_t(sk_try) * kb < 2ull * clusters) return;
-    sk = sk_try;
-    dp = tiles - sk;
+uint32_t streamk_rounds_cost(uint32_t sk, uint32_t split, uint32_t clusters, uint32_t kb) {
+    // K blocks of tensor time the slice phase takes: rounds x (slice length + per-slice overhead: draining the
+    // accumulator into the workspace and, for the last arriver, reading the other slices back)
+    constexpr uint32_t kSliceOverheadKb = 6;
+    const uint32_t rounds = ceil_div(sk * split, clusters);
+    return rounds * (ceil_div(kb, split) + kSliceOverheadKb);
 }
 
-uint64_t streamk_partial_bytes(uint32_t clusters, uint32_t cta_group, uint32_t block_n) {
-    return uint64_t(clusters) * 2 * cta_group * 128 * block_n * 4;
+void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t want_split, uint32_t& dp, uint32_t& sk,
+                   uint32_t& split) {
+    const uint32_t rem = tiles % clusters;
+    dp = tiles;
+    sk = 0;
+    split = 1;
+    if (rem == 0 || kb < 4) return;
+    uint32_t best = 0, best_cost = kb;   // cost of leaving the ragged wave whole
+    if (want_split >= 2) {
+        best = std::min(want_split, std::min(kb, 16u));
+    } else {
+        for (uint32_t s = 2; s <= 8 && s <= kb; ++s) {
+            const uint32_t cost = streamk_rounds_cost(rem, s, clusters, kb);
+            if (cost < best_cost) { best_cost = cost; best = s; }
+        }
+    }
+    if (best < 2) return;
+    sk = rem;
+    dp = tiles - rem;
+    split = best;
+}
+
+uint64_t streamk_partial_bytes(uint32_t sk, uint32_t split, uint32_t cta_group, uint32_t block_n) {
+    return uint64_t(sk) * split * cta_group * 128 * block_n * 4;
 }
 
 PadLayout pad_layout(const DgaTilingPlan& p) {
@@ -252,13 +270,15 @@ int finalize_plan(DgaTilingPlan& p) {
             p.paddingTagC = 0;   // the reduce kernel stores C with plain st.global: any pitch will do
         } else if (p.kernelSerial == DGA_KERNEL_STREAMK) {
             const uint32_t clusters = hw.smCount / cta;
-            uint32_t dp, sk;
-            streamk_split(tiles, clusters, ceil_div(p.k, 128 / in_b), dp, sk);
+            uint32_t dp, sk, split;
+            streamk_split(tiles, clusters, ceil_div(p.k, 128 / in_b), p.splitkFactor, dp, sk, split);
             if (sk == 0) {
                 p.kernelSerial = tiles <= clusters ? DGA_KERNEL_SMALL : DGA_KERNEL_COMMON;
+                p.splitkFactor = 1;
             } else {
-                p.blockDim = clusters * cta;
-                p.workspaceBytes = streamk_partial_bytes(clusters, cta, p.n1) + ((uint64_t(sk) * cta * 4 + 255) & ~255ull);
+                p.splitkFactor = uint16_t(split);
+                p.blockDim = uint32_t(std::min<uint64_t>(uint64_t(dp) + uint64_t(sk) * split, clusters)) * cta;
+                p.workspaceBytes = streamk_partial_bytes(sk, split, cta, p.n1) + ((uint64_t(sk) * cta * 4 + 255) & ~255ull);
             }
         } else if (p.kernelSerial != DGA_KERNEL_SMALL && p.kernelSerial != DGA_KERNEL_COMMON) {
             set_error("kernel variant " + std::to_string(int(p.kernelSerial)) + " is not built");

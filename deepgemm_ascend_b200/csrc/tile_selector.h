@@ -45,11 +45,14 @@ int finalize_plan(DgaTilingPlan& plan);
 int select_kernel_with_cache(DgaTilingPlan& plan);
 
 // Stream-K decomposition of `tiles` output tiles of `kb` K blocks over `clusters` clusters: the first `dp` tiles are
-// walked whole (one per cluster and wave), the K blocks of the last `sk` tiles are dealt out evenly.  sk == 0 when
-// the tiles already fill whole waves or the slices would be too thin.
-void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t& dp, uint32_t& sk);
-// Workspace layout of the stream-K variant: fp32 partial slots, then the per-tile arrival counters.
-uint64_t streamk_partial_bytes(uint32_t clusters, uint32_t cta_group, uint32_t block_n);
+// walked whole (one per cluster and wave); each of the last `sk` tiles (the ragged wave) is cut into `split` K slices
+// with aligned boundaries, dealt out round-robin.  want_split >= 2 forces the slice count (hand-set plans), else the
+// count that minimises rounds x slice length is chosen; sk == 0 when the tiles already fill whole waves or no
+// slice count beats leaving the last wave whole.
+void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t want_split, uint32_t& dp, uint32_t& sk,
+                   uint32_t& split);
+// Workspace layout of the stream-K variant: one fp32 partial slot per slice and CTA rank, then the per-tile counters.
+uint64_t streamk_partial_bytes(uint32_t sk, uint32_t split, uint32_t cta_group, uint32_t block_n);
 
 // Multicore split-K (DGA_KERNEL_SPLITK_REDUCE): row pitch (floats) and bytes of the [split][m][pitch] fp32 partial slabs.
 inline uint32_t splitk_ws_pitch(uint32_t n) { return round_up(n, 32); }

@@ -85,6 +85,11 @@ ACLNN_CASES = [
     (300, 520, 1992, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 1, "n1": 64}),
     (2048, 4096, 2048, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 256}),
     (640, 1024, 1024, torch.float16, 0, {"kernelSerial": 4, "ctaGroup": 2, "n1": 128}),
+    # hand-set slice counts (splitkFactor of a stream-K plan), incl. one that does not divide the K blocks
+    (512, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 256, "splitkFactor": 2}),
+    (2048, 4096, 2048, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 256, "splitkFactor": 4}),
+    (1000, 1000, 1000, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 1, "n1": 128, "splitkFactor": 3}),
+    (384, 512, 4096, torch.float16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 64, "splitkFactor": 7}),
     # multicore split-K + reduce kernel (the reference's declared kernel type 3 + StreamkReduceAdd)
     (512, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 5, "ctaGroup": 2, "n1": 256, "splitkFactor": 2}),
     (128, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 5, "ctaGroup": 1, "n1": 256, "splitkFactor": 8}),
