@@ -414,18 +414,11 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
             const uint64_t part = streamk_partial_bytes(gp.sk_tiles, split, cta, p.n1);
             gp.sk_partials = static_cast<float*>(workspace);
             gp.sk_sems = reinterpret_cast<int32_t*>(static_cast<char*>(workspace) + part);
-            // The counters are left at zero by the kernel (the last slice of a tile resets its counter), so they
-            // only need clearing the first time a workspace region is used for them.
-            static std::mutex mu;
-            static const void* cleared_ptr = nullptr;
-            static uint64_t cleared_bytes = 0;
-            const uint64_t sem_bytes = uint64_t(gp.sk_tiles) * cta * 4;
-            std::lock_guard<std::mutex> lock(mu);
-            if (cleared_ptr != gp.sk_sems || cleared_bytes < sem_bytes) {
-                DGA_CUDA(cudaMemsetAsync(gp.sk_sems, 0, sem_bytes, stream));
-                cleared_ptr = gp.sk_sems;
-                cleared_bytes = sem_bytes;
-            }
+            // "partial is ready" flags carry a per-launch nonce (GemmParams::sk_sems): no clearing launch, whatever
+            // bytes the caller's workspace holds
+            static std::atomic<uint32_t> launch_seq{0};
+            const uint32_t seq = launch_seq.fetch_add(1, std::memory_order_relaxed) + 1;
+            gp.sk_nonce = int32_t((seq * 2654435761u) | 1u);
         }
     }
     static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();

@@ -68,7 +68,11 @@ struct GemmParams {
     uint32_t split_k;
     const int32_t* group_index;
     float* sk_partials;      // [slice item][cta rank][128][block_n] fp32
-    int32_t* sk_sems;        // [sk tile][cta rank] arrival counters, zero on entry and on exit
+    int32_t* sk_sems;        // [slice item][cta rank] "partial is in its slot" flags: the giver stores sk_nonce, the
+                             // owner waits for it and stores 0 back.  A per-launch nonce instead of a counter so
+                             // that a workspace the caller recycled (arbitrary bytes) needs no clearing launch and
+                             // cannot stall the owner; the write-back of 0 keeps CUDA-graph replays (same nonce) right
+    int32_t sk_nonce;        // non-zero
 };
 
 // N-sharded execution (BASELINE config 5): besides its own C, a rank's epilogue stores every finished chunk
@@ -495,7 +499,6 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
         const uint32_t epi_tid = threadIdx.x - 128;          // 0..127 == accumulator row == TMEM lane
         const uint32_t lane_base = (warp & 3) * 32;          // tcgen05.ld lane window of this warp
         uint32_t iter = 0, buf = 0;
-        volatile uint32_t* sk_bcast = tmem_ptr_smem + 1;       // arrival count broadcast inside the epilogue warps
         // one 32-column chunk of this CTA's rows: registers -> staging smem -> TMA store
         const bool wide = p.epi_cols == 64;
         int32_t zb = 0;   // batch entry of the tile being stored (mode 1)
@@ -563,68 +566,105 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                     store_chunk(v, m0, n0 + c * kEpiCols, c, c + 1 == chunks);
                 }
             } else {
-                // ---- stream-K slice: fp32 partial -> workspace; the last slice of the tile to arrive adds them up
-                // in slice order (deterministic) and stores the tile.
+                // ---- stream-K slice.  Slices 0 .. S-2 of a tile ("givers") leave their fp32 partial in their
+                // workspace slot and bump the tile's counter; slice S-1 (the "owner", fixed, so the summation order
+                // is too) waits for S-1 arrivals, then adds the slots in slice order and its own accumulator, still
+                // in TMEM, last.  No deadlock: a slice only ever waits for slices with a smaller item index, every
+                // cluster walks its items in increasing order, and the whole grid is resident (<= one CTA per SM).
                 const uint64_t slot_floats = static_cast<uint64_t>(kBlockM) * p.block_n;
-                auto slot_of = [&](uint32_t item) {
-                    return p.sk_partials + (static_cast<uint64_t>(item) * kCta + cta_rank) * slot_floats;
-                };
-                const uint32_t first = (w.tile - p.dp_tiles) * p.split_k, last = first + p.split_k - 1;
+                const uint32_t split = p.split_k;
+                const uint32_t first = (w.tile - p.dp_tiles) * split;      // item index of slice 0
+                const uint32_t slice = w.item - first;
+                auto flag_of = [&](uint32_t item) { return p.sk_sems + item * kCta + cta_rank; };
                 // slot layout [chunk][4-column group][row] of 16-byte words: a warp's 32 rows are contiguous
-                uint4* mine = reinterpret_cast<uint4*>(slot_of(w.item)) + epi_tid;
-                for (uint32_t c = 0; c < chunks; ++c) {
-                    uint32_t v[32];
-                    ptx::tmem_ld_32x32(taddr + c * kEpiCols, v);
-                    ptx::tmem_ld_wait();
-                    if (c + 1 == chunks) release_tmem();
-#pragma unroll
-                    for (uint32_t j = 0; j < 8; ++j)
-                        __stcg(mine + (c * 8 + j) * kBlockM, make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
-                }
-                __threadfence();
-                ptx::named_bar_sync(1, 128);
-                int32_t* sem = p.sk_sems + (w.tile - p.dp_tiles) * kCta + cta_rank;
-                if (epi_tid == 0) *sk_bcast = static_cast<uint32_t>(atomicAdd(sem, 1));
-                ptx::named_bar_sync(1, 128);
-                const uint32_t arrived = *sk_bcast;
-                if (arrived == last - first && (p.debug & 8)) {
-                    if (epi_tid == 0) *sem = 0;   // isolation: skip the reduction
-                } else if (arrived == last - first) {
-                    __threadfence();
+                auto slot_of = [&](uint32_t item) {
+                    return reinterpret_cast<uint4*>(p.sk_partials + (static_cast<uint64_t>(item) * kCta + cta_rank) * slot_floats) + epi_tid;
+                };
+                if (slice + 1 != split) {
+                    uint4* mine = slot_of(w.item);
                     for (uint32_t c = 0; c < chunks; ++c) {
-                        float acc[32];
+                        uint32_t v[32];
+                        ptx::tmem_ld_32x32(taddr + c * kEpiCols, v);
+                        ptx::tmem_ld_wait();
+                        if (c + 1 == chunks) release_tmem();
 #pragma unroll
-                        for (uint32_t j = 0; j < 32; ++j) acc[j] = 0.f;
-                        // three slices at a time: 24 independent 16-byte loads in flight per thread hide the L2 latency
-                        for (uint32_t q = first; q <= last; q += 3) {
-                            uint4 t4[3][8];
-#pragma unroll
-                            for (uint32_t i = 0; i < 3; ++i) {
-                                if (q + i <= last) {
-                                    const uint4* src = reinterpret_cast<const uint4*>(slot_of(q + i)) + epi_tid + c * 8 * kBlockM;
-#pragma unroll
-                                    for (uint32_t j = 0; j < 8; ++j) t4[i][j] = __ldcg(src + j * kBlockM);
-                                }
-                            }
-#pragma unroll
-                            for (uint32_t i = 0; i < 3; ++i) {
-                                if (q + i <= last) {
-#pragma unroll
-                                    for (uint32_t j = 0; j < 8; ++j) {
-                                        acc[4 * j + 0] += __uint_as_float(t4[i][j].x);
-                                        acc[4 * j + 1] += __uint_as_float(t4[i][j].y);
-                                        acc[4 * j + 2] += __uint_as_float(t4[i][j].z);
-                                        acc[4 * j + 3] += __uint_as_float(t4[i][j].w);
-                                    }
-                                }
+                        for (uint32_t j = 0; j < 8; ++j)
+                            __stcg(mine + (c * 8 + j) * kBlockM, make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
+                    }
+                    __threadfence();
+                    ptx::named_bar_sync(1, 128);
+                    if (epi_tid == 0 && !(p.debug & 8)) atomicExch(flag_of(w.item), p.sk_nonce);
+                } else {
+                    const uint32_t others = (p.debug & 8) ? 0u : split - 1;   // debug 8: skip the reduction
+                    if (others != 0) {
+                        if (epi_tid < others) {
+                            // every giver is resident and never waits, so this ends; the deadline turns a broken
+                            // invariant into a launch failure instead of a hung device
+                            const volatile int32_t* flag = flag_of(first + epi_tid);
+                            const unsigned long long deadline = ptx::globaltimer() + 2000000000ull;
+                            while (*flag != p.sk_nonce) {
+                                __nanosleep(64);
+                                if (ptx::globaltimer() > deadline) __trap();
                             }
                         }
-                        uint32_t v[32];
-#pragma unroll
-                        for (uint32_t j = 0; j < 32; ++j) v[j] = __float_as_uint(acc[j]);
-                        store_chunk(v, m0, n0 + c * kEpiCols, c, c + 1 == chunks);
+                        ptx::named_bar_sync(1, 128);
+                        __threadfence();
                     }
-                    if (epi_tid == 0) *sem = 0;   // ready for the next launch
+                    // software pipeline over (chunk, giver slice) pairs: the loads of pair i + 1 fly while pair i
+                    // is added; two register sets, every index a compile-time constant
+                    const uint32_t pairs = chunks * others;
+                    uint4 ld_a[8], ld_b[8];
+                    float acc[32];
+                    auto fetch = [&](uint4 (&dst)[8], uint32_t i) __attribute__((always_inline)) {
+                        const uint32_t c = i / others, sl = i - c * others;
+                        const uint4* src = slot_of(first + sl) + c * 8 * kBlockM;
+#pragma unroll
+                        for (uint32_t j = 0; j < 8; ++j) dst[j] = __ldcg(src + j * kBlockM);
+                    };
+                    auto finish_chunk = [&](uint32_t c) __attribute__((always_inline)) {
+                        uint32_t own[32];
+                        ptx::tmem_ld_32x32(taddr + c * kEpiCols, own);
+                        ptx::tmem_ld_wait();
+                        if (c + 1 == chunks) release_tmem();
+#pragma unroll
+                        for (uint32_t j = 0; j < 32; ++j) own[j] = __float_as_uint(acc[j] + __uint_as_float(own[j]));
+                        store_chunk(own, m0, n0 + c * kEpiCols, c, c + 1 == chunks);
+                    };
+                    auto consume = [&](const uint4 (&src)[8], uint32_t i) __attribute__((always_inline)) {
+                        const uint32_t c = i / others, sl = i - c * others;
+                        if (sl == 0) {
+#pragma unroll
+                            for (uint32_t j = 0; j < 32; ++j) acc[j] = 0.f;
+                        }
+#pragma unroll
+                        for (uint32_t j = 0; j < 8; ++j) {
+                            acc[4 * j + 0] += __uint_as_float(src[j].x);
+                            acc[4 * j + 1] += __uint_as_float(src[j].y);
+                            acc[4 * j + 2] += __uint_as_float(src[j].z);
+                            acc[4 * j + 3] += __uint_as_float(src[j].w);
+                        }
+                        if (sl + 1 == others) finish_chunk(c);
+                    };
+                    if (pairs == 0) {
+#pragma unroll
+                        for (uint32_t j = 0; j < 32; ++j) acc[j] = 0.f;
+                        for (uint32_t c = 0; c < chunks; ++c) finish_chunk(c);
+                    } else {
+                        fetch(ld_a, 0);
+#pragma unroll 1
+                        for (uint32_t i = 0; i < pairs; i += 2) {
+                            if (i + 1 < pairs) fetch(ld_b, i + 1);
+                            consume(ld_a, i);
+                            if (i + 1 < pairs) {
+                                if (i + 2 < pairs) fetch(ld_a, i + 2);
+                                consume(ld_b, i + 1);
+                            }
+                        }
+                    }
+                    if (others != 0) {
+                        ptx::named_bar_sync(1, 128);   // every thread has read the slots
+                        if (epi_tid < others) *flag_of(first + epi_tid) = 0;   // a replay with the same nonce starts clean
+                    }
                 }
             }
         }

@@ -278,7 +278,7 @@ int finalize_plan(DgaTilingPlan& p) {
             } else {
                 p.splitkFactor = uint16_t(split);
                 p.blockDim = uint32_t(std::min<uint64_t>(uint64_t(dp) + uint64_t(sk) * split, clusters)) * cta;
-                p.workspaceBytes = streamk_partial_bytes(sk, split, cta, p.n1) + ((uint64_t(sk) * cta * 4 + 255) & ~255ull);
+                p.workspaceBytes = streamk_partial_bytes(sk, split, cta, p.n1) + ((uint64_t(sk) * split * cta * 4 + 255) & ~255ull);
             }
         } else if (p.kernelSerial != DGA_KERNEL_SMALL && p.kernelSerial != DGA_KERNEL_COMMON) {
             set_error("kernel variant " + std::to_string(int(p.kernelSerial)) + " is not built");
@@ -357,12 +357,25 @@ int select_kernel(DgaTilingPlan& p) {
     const uint32_t pairs = platform().smCount / 2;
     const uint32_t tiles256 = ceil_div(p.m, 256) * ceil_div(p.n, 256);
     const uint32_t kb_all = ceil_div(p.k, 128 / in_b);
+    const uint32_t tiles128 = ceil_div(p.n, 128);
     const uint32_t split_r = std::min<uint32_t>(std::min<uint32_t>(8, pairs / std::max(1u, tiles256)), kb_all / 14);
     if (sbest.split != 0 && (sbest.us < best.us || p.m <= 128)) {
         p.kernelSerial = DGA_KERNEL_SPLITK;
         p.splitkFactor = static_cast<uint16_t>(sbest.split);
         p.stages = static_cast<uint8_t>(sbest.stages);
         p.estTimeUs = sbest.us;
+    } else if (p.m > 128 && p.m <= 256 && 2 * tiles128 <= pairs && 8 * tiles128 >= 3 * pairs && kb_all >= 32) {
+        // Stream-K (role of PaddingStreamkMatmulKernel): one 256-row block, 256 x 128 pair tiles cut into two K
+        // slices fill 75-100 % of the pairs in a single round, and the fix-up of a 128-wide tile is short.  Measured
+        // on B200 (profiles/r01_streamk_aligned_sweep.log), M=256 / 192: N=4096, K=7168: 21.9 / 21.7 us vs 24.8 /
+        // 23.0 for split-K + reduce; N=4096, K=2048: 13.2 / 13.1 vs 18.9 / 17.3 us.  Outside that window (N=2048 or
+        // N=7168) it loses, and so does every shape with more than one 256-row block.
+        p.kernelSerial = DGA_KERNEL_STREAMK;
+        p.ctaGroup = 2;
+        p.n1 = 128;
+        p.stages = 0;
+        p.splitkFactor = 2;
+        p.estTimeUs = best.us;
     } else if (p.m > 128 && tiles256 * 4 <= pairs && split_r >= 2) {
         p.kernelSerial = DGA_KERNEL_SPLITK_REDUCE;
         p.ctaGroup = 2;

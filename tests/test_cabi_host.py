@@ -175,9 +175,15 @@ def test_selector_decision_structure(dga):
     waves = -(-tiles // 74)
     assert tiles / (waves * 74) > 0.95, "wave quantisation: BalanceWorkload's job (utils.cpp:28-40)"
     # under-filled and long K -> multicore split-K + reduce (the reference's declared kernel type 3 + StreamkReduceAdd)
-    p = dga.select_kernel(256, 4096, 7168)
-    assert p["kernelSerial"] == 5 and p["ctaGroup"] == 2 and p["n1"] == 256 and p["splitkFactor"] == 4
-    assert p["workspaceBytes"] == 4 * 256 * 4096 * 4 and p["blockDim"] == 128
+    p = dga.select_kernel(256, 2048, 7168)
+    assert p["kernelSerial"] == 5 and p["ctaGroup"] == 2 and p["n1"] == 256 and p["splitkFactor"] == 8
+    assert p["workspaceBytes"] == 8 * 256 * 2048 * 4 and p["blockDim"] == 128
+    # one 256-row block whose 128-wide tiles, cut in two K slices, fill the pairs in one round -> stream-K (the
+    # reference's PaddingStreamk pick at its own ragged-wave shapes, select_kernel.cpp:290-301)
+    for m in (192, 256):
+        p = dga.select_kernel(m, 4096, 7168)
+        assert p["kernelSerial"] == 4 and p["ctaGroup"] == 2 and p["n1"] == 128 and p["splitkFactor"] == 2
+        assert p["blockDim"] == 128 and p["workspaceBytes"] >= 64 * 2 * 128 * 128 * 4
     assert dga.select_kernel(512, 4096, 7168)["kernelSerial"] in (0, 1)      # enough tiles: single pass
     assert dga.select_kernel(256, 4096, 512)["kernelSerial"] in (0, 1)       # short K: nothing to split
     # at most one tile per cluster -> Small (select_kernel.cpp:285-289)

@@ -77,6 +77,9 @@ ACLNN_CASES = [
     (16, 256, 512, torch.bfloat16, 1, {"kernelSerial": 3, "splitkFactor": 2}),
     (16, 584, 2016, torch.float16, 1, {}),                   # custom_catlass demo shape 16x578x2014, 16 B-aligned
     (512, 4096, 7168, torch.bfloat16, 1, {}),
+    (256, 4096, 7168, torch.bfloat16, 1, {}),                # the selector's stream-K window (one 256-row block)
+    (192, 4096, 2048, torch.bfloat16, 1, {}),
+    (200, 4000, 4096, torch.bfloat16, 0, {}),
     (2048, 4096, 2048, torch.bfloat16, 1, {}),
     # stream-K variant (role of PaddingStreamkMatmulKernel): K blocks of the ragged wave dealt out to every cluster
     (512, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 256}),
@@ -89,7 +92,7 @@ ACLNN_CASES = [
     (512, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 256, "splitkFactor": 2}),
     (2048, 4096, 2048, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 256, "splitkFactor": 4}),
     (1000, 1000, 1000, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 1, "n1": 128, "splitkFactor": 3}),
-    (384, 512, 4096, torch.float16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 64, "splitkFactor": 7}),
+    (384, 512, 4096, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 64, "splitkFactor": 7}),
     # multicore split-K + reduce kernel (the reference's declared kernel type 3 + StreamkReduceAdd)
     (512, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 5, "ctaGroup": 2, "n1": 256, "splitkFactor": 2}),
     (128, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 5, "ctaGroup": 1, "n1": 256, "splitkFactor": 8}),
@@ -209,6 +212,50 @@ def test_rtc_batched(dga):
     for i in range(b):
         ref = orc.golden_fp64(x[i].float().cpu().numpy(), y[i].float().cpu().numpy())
         assert orc.max_rel_err(out[i].cpu().numpy(), ref) < 1e-5
+
+
+def test_stream_k_tolerates_a_dirty_workspace_and_graph_replay(dga):
+    """The selector's stream-K plan keeps "partial is ready" flags in the caller's workspace; whatever bytes the
+    workspace held before (all ones, random, the leftovers of a previous run) the result is the same, and a captured
+    launch replays correctly (the flags are written back to zero)."""
+    m, n, k = 256, 4096, 2048
+    assert dga.select_kernel(m, n, k)["kernelSerial"] == 4
+    a, b = _inputs(m, n, k, torch.bfloat16, seed=21)
+    ta, w = _to_dev(a, torch.bfloat16), _to_dev(b.T, torch.bfloat16)
+    ref = orc.golden_fp64(a, b)
+    out = torch.zeros((m, n), dtype=torch.bfloat16, device=DEV)
+    ws_bytes, ex = dga.get_workspace_size(ta, w.t(), out)
+    dga.destroy_executor(ex)
+    assert ws_bytes > 0
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    gen = torch.Generator(device=DEV).manual_seed(1)
+    results = []
+    for fill in ("ones", "random", "leftover", "leftover"):
+        if fill == "ones":
+            ws.fill_(255)
+        elif fill == "random":
+            ws.copy_(torch.randint(0, 256, (ws_bytes,), dtype=torch.uint8, device=DEV, generator=gen))
+        out.zero_()
+        _, ex = dga.get_workspace_size(ta, w.t(), out)
+        dga.execute(ws, ws_bytes, ex)
+        torch.cuda.synchronize()
+        results.append(out.float().cpu().numpy())
+        assert orc.max_rel_err(results[-1], ref) <= 1e-2
+    assert all(np.array_equal(results[0], r) for r in results[1:])   # fixed summation order: bit-identical
+    exe = dga.Executor(ta, w.t(), out)
+    stream = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(stream):
+        exe(stream)
+        stream.synchronize()
+        with torch.cuda.graph(graph, stream=stream):
+            exe(stream)
+    for _ in range(3):
+        out.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert np.array_equal(out.float().cpu().numpy(), results[0])
+    exe.close()
 
 
 def test_executor_repeatable_and_graph_capturable(dga):
