@@ -407,8 +407,8 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
     if (p.kernelSerial == DGA_KERNEL_STREAMK) {
         const uint32_t clusters = platform().smCount / cta;
         uint32_t split = 1;
-        streamk_split(gp.num_m_blocks * gp.num_n_blocks, clusters, gp.k_blocks, p.splitkFactor, gp.dp_tiles, gp.sk_tiles,
-                      split);
+        streamk_split(gp.num_m_blocks * gp.num_n_blocks, clusters, gp.k_blocks, p.n1, p.splitkFactor, gp.dp_tiles,
+                      gp.sk_tiles, split);
         gp.split_k = split;
         if (gp.sk_tiles != 0) {
             const uint64_t part = streamk_partial_bytes(gp.sk_tiles, split, cta, p.n1);

@@ -157,16 +157,20 @@ bool aligned16(uint64_t elems, uint32_t bytes) { return (elems * bytes) % 16 == 
 
 }  // namespace
 
-uint32_t streamk_rounds_cost(uint32_t sk, uint32_t split, uint32_t clusters, uint32_t kb) {
-    // K blocks of tensor time the slice phase takes: rounds x (slice length + per-slice overhead: draining the
-    // accumulator into the workspace and, for the last arriver, reading the other slices back)
-    constexpr uint32_t kSliceOverheadKb = 6;
-    const uint32_t rounds = ceil_div(sk * split, clusters);
-    return rounds * (ceil_div(kb, split) + kSliceOverheadKb);
+uint32_t streamk_overhead_kb(uint32_t block_n) {
+    // the exposed fix-up chain (giver drains and writes, fence + flag, owner's adding pass) is ~5 us longer than a
+    // plain epilogue: ~7500 clocks, in units of one K block of this tile (2 * block_n clocks)
+    return std::max(4u, 7500u / (2u * std::max(32u, block_n)));
 }
 
-void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t want_split, uint32_t& dp, uint32_t& sk,
-                   uint32_t& split) {
+uint32_t streamk_rounds_cost(uint32_t sk, uint32_t split, uint32_t clusters, uint32_t kb, uint32_t overhead_kb) {
+    // K blocks of tensor time the slice phase takes: rounds x (slice length + per-slice overhead)
+    const uint32_t rounds = ceil_div(sk * split, clusters);
+    return rounds * (ceil_div(kb, split) + overhead_kb);
+}
+
+void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t block_n, uint32_t want_split, uint32_t& dp,
+                   uint32_t& sk, uint32_t& split) {
     const uint32_t rem = tiles % clusters;
     dp = tiles;
     sk = 0;
@@ -177,7 +181,7 @@ void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t want
         best = std::min(want_split, std::min(kb, 16u));
     } else {
         for (uint32_t s = 2; s <= 8 && s <= kb; ++s) {
-            const uint32_t cost = streamk_rounds_cost(rem, s, clusters, kb);
+            const uint32_t cost = streamk_rounds_cost(rem, s, clusters, kb, streamk_overhead_kb(block_n));
             if (cost < best_cost) { best_cost = cost; best = s; }
         }
     }
@@ -271,7 +275,7 @@ int finalize_plan(DgaTilingPlan& p) {
         } else if (p.kernelSerial == DGA_KERNEL_STREAMK) {
             const uint32_t clusters = hw.smCount / cta;
             uint32_t dp, sk, split;
-            streamk_split(tiles, clusters, ceil_div(p.k, 128 / in_b), p.splitkFactor, dp, sk, split);
+            streamk_split(tiles, clusters, ceil_div(p.k, 128 / in_b), p.n1, p.splitkFactor, dp, sk, split);
             if (sk == 0) {
                 p.kernelSerial = tiles <= clusters ? DGA_KERNEL_SMALL : DGA_KERNEL_COMMON;
                 p.splitkFactor = 1;
@@ -323,6 +327,9 @@ int select_kernel(DgaTilingPlan& p) {
     // --- persistent kernel candidates (wave balancing over 74 pairs / 148 CTAs)
     Cand best{0, 0, 0, 0, 0, 1e30};
     for (uint32_t cta = 2; cta >= 1; --cta) {
+        // up to 128 rows a pair tile spends half of its tensor work on rows that do not exist (audit: M=128,
+        // N=32768, K=512: 10.0 us single-CTA vs 11.8 us pair; N=24576, K=1536: 17.5 vs 19.8 us)
+        if (cta == 2 && p.m <= 128) continue;
         const uint32_t step = (p.layoutTagB == 0) ? 64 * cta : 16 * cta;
         for (uint32_t bn = 256; bn >= step && bn >= 32; bn -= step) {
             if (bn % 32 != 0) continue;  // epilogue works in 32-column chunks
@@ -359,7 +366,12 @@ int select_kernel(DgaTilingPlan& p) {
     const uint32_t kb_all = ceil_div(p.k, 128 / in_b);
     const uint32_t tiles128 = ceil_div(p.n, 128);
     const uint32_t split_r = std::min<uint32_t>(std::min<uint32_t>(8, pairs / std::max(1u, tiles256)), kb_all / 14);
-    if (sbest.split != 0 && (sbest.us < best.us || p.m <= 128)) {
+    // ... except where the weight is wide and K short (N >= 6144, K <= 3072 at 16 bit): the decode kernel's CTAs then
+    // run a handful of K blocks each and the persistent kernel has enough tiles to fill the machine (selector audit,
+    // profiles/r01c_selector_audit.log: M=128, N=7168, K=2048: 12.0 vs 13.4 us; N=24576, K=1536: 17.5 vs 20.5 us;
+    // N=32768, K=512: 10.0 vs 13.0 us).
+    const bool wide_short = p.m > 64 && tiles128 >= 48 && kb_all <= 48;
+    if (sbest.split != 0 && ((p.m <= 128 && !wide_short) || (p.m > 128 && sbest.us < best.us))) {
         p.kernelSerial = DGA_KERNEL_SPLITK;
         p.splitkFactor = static_cast<uint16_t>(sbest.split);
         p.stages = static_cast<uint8_t>(sbest.stages);
@@ -385,6 +397,20 @@ int select_kernel(DgaTilingPlan& p) {
         p.estTimeUs = best.us;
     } else {
         fill_common(p, best);
+        // Stream-K on the chosen tile when the last wave is ragged and K is long enough to pay for the fix-up
+        // (audit: 2048 x 7168 x 16384: 279 vs 326 us; 4096 x 7168 x 16384: 575 vs 601 us; 4096 x 4096 x 7168: 143 vs 147 us).
+        const uint32_t clusters = platform().smCount / best.cta;
+        const uint32_t full = best.tiles / clusters, rem = best.tiles % clusters;
+        if (best.cta == 2 && full >= 1 && rem != 0 && 2 * rem <= clusters && kb_all >= 64) {
+            // two slices per ragged tile, one round: the only configuration the audit shows winning (more slices or
+            // a second round and the owners' adding passes eat the gain: 1024 x 7168 x 16384 with 5 slices: 234 vs 148 us)
+            const uint32_t cost = streamk_rounds_cost(rem, 2, clusters, kb_all, streamk_overhead_kb(best.bn));
+            if (cost < kb_all && double(kb_all - cost) >= 0.03 * double(full + 1) * kb_all) {
+                p.kernelSerial = DGA_KERNEL_STREAMK;
+                p.splitkFactor = 2;
+                p.stages = 0;
+            }
+        }
     }
     // PaddingCommon survives only as a leading-dimension repack (padding_common_matmul_kernel.h:64-82): the tags
     // above describe contiguous operands; the launch path re-derives them from the caller's actual strides.

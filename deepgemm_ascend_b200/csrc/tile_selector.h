@@ -49,8 +49,8 @@ int select_kernel_with_cache(DgaTilingPlan& plan);
 // with aligned boundaries, dealt out round-robin.  want_split >= 2 forces the slice count (hand-set plans), else the
 // count that minimises rounds x slice length is chosen; sk == 0 when the tiles already fill whole waves or no
 // slice count beats leaving the last wave whole.
-void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t want_split, uint32_t& dp, uint32_t& sk,
-                   uint32_t& split);
+void streamk_split(uint32_t tiles, uint32_t clusters, uint32_t kb, uint32_t block_n, uint32_t want_split, uint32_t& dp,
+                   uint32_t& sk, uint32_t& split);
 // Workspace layout of the stream-K variant: one fp32 partial slot per slice and CTA rank, then the per-tile counters.
 uint64_t streamk_partial_bytes(uint32_t sk, uint32_t split, uint32_t cta_group, uint32_t block_n);
 

@@ -132,7 +132,7 @@ def matmul_with_plan(self, mat2, out, stream=None, **fields):
     a, b, c = acl_tensor(self), acl_tensor(mat2), acl_tensor(out)
     global _PLAN_WS
     if _PLAN_WS is None or _PLAN_WS.device != out.device:
-        _PLAN_WS = torch.empty(64 << 20, dtype=torch.uint8, device=out.device)   # covers every stream-K plan
+        _PLAN_WS = torch.empty(256 << 20, dtype=torch.uint8, device=out.device)   # covers every stream-K / split-K plan
     check(lib.dgaMatmulWithPlan(ctypes.byref(a), ctypes.byref(b), ctypes.byref(c), ctypes.byref(plan),
                                 ctypes.c_void_p(_PLAN_WS.data_ptr()), _PLAN_WS.numel(), _stream_ptr(stream)),
           "dgaMatmulWithPlan")

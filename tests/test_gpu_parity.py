@@ -159,6 +159,16 @@ def test_config3_sweep_full_size(dga, m):
     _sampled_full_size(dga, m, 4096, 7168, seed=m)
 
 
+@pytest.mark.parametrize("m,n,k,serial", [(4096, 4096, 7168, 4),      # ragged last wave, long K -> stream-K, 2 slices
+                                          (2048, 7168, 16384, 4),
+                                          (128, 7168, 2048, 1),       # wide weight, short K -> single-CTA tiles, not decode
+                                          (128, 24576, 1536, 1)])
+def test_selector_audit_shapes_full_size(dga, m, n, k, serial):
+    """Shapes whose plan comes from the selector audit (profiles/r01c_selector_audit.log), through the default path."""
+    assert dga.select_kernel(m, n, k)["kernelSerial"] == serial
+    _sampled_full_size(dga, m, n, k, seed=m + n)
+
+
 def test_config5_one_shard_full_size(dga):
     """BASELINE config 5 as one rank of eight sees it: M=16384, N=57344/8, K=7168."""
     _sampled_full_size(dga, 16384, 7168, 7168, seed=5)
