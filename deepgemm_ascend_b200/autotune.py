@@ -26,7 +26,7 @@ import os
 from . import _lib
 from ._lib import lib, check
 
-KERNEL_COMMON, KERNEL_SPLITK, KERNEL_STREAMK = 0, 3, 4
+KERNEL_COMMON, KERNEL_SPLITK, KERNEL_STREAMK, KERNEL_SPLITK_REDUCE = 0, 3, 4, 5
 ERROR_TOLERANCE = 1e-2   # max relative error of a candidate against the fp32 golden on sampled rows
 
 
@@ -46,6 +46,11 @@ def candidate_plans(m, n, k, layout_b=1):
                 for split in (0, 2, 4):    # 0 = slice count chosen by streamk_split
                     out.append({"kernelSerial": KERNEL_STREAMK, "ctaGroup": cta, "n1": n1, "stages": 0,
                                 "splitkFactor": split})
+    if m > 128 and -(-m // 256) * -(-n // 256) * 4 <= 74:
+        for split in (2, 4, 6, 8):   # multicore split-K + reduce kernel on 256 x 256 pair tiles
+            if -(-k // 64) >= 14 * split // 2:
+                out.append({"kernelSerial": KERNEL_SPLITK_REDUCE, "ctaGroup": 2, "n1": 256, "stages": 0,
+                            "splitkFactor": split})
     if m <= 256 and layout_b == 1:
         for split in (1, 2, 4, 8):
             if -(-k // 64) < split:

@@ -365,26 +365,43 @@ int select_kernel(DgaTilingPlan& p) {
     const uint32_t tiles256 = ceil_div(p.m, 256) * ceil_div(p.n, 256);
     const uint32_t kb_all = ceil_div(p.k, 128 / in_b);
     const uint32_t tiles128 = ceil_div(p.n, 128);
-    const uint32_t split_r = std::min<uint32_t>(std::min<uint32_t>(8, pairs / std::max(1u, tiles256)), kb_all / 14);
+    // slices of >= 8 K blocks once K >= 3584 (audit: 256 x 1024 x 4096 with 8 slices 12.1 us vs 13.6 with 4), >= 14 below
+    const uint32_t split_r = std::min<uint32_t>(std::min<uint32_t>(8, pairs / std::max(1u, tiles256)),
+                                                kb_all >= 56 ? kb_all / 8 : kb_all / 14);
     // ... except where the weight is wide and K short (N >= 6144, K <= 3072 at 16 bit): the decode kernel's CTAs then
     // run a handful of K blocks each and the persistent kernel has enough tiles to fill the machine (selector audit,
     // profiles/r01c_selector_audit.log: M=128, N=7168, K=2048: 12.0 vs 13.4 us; N=24576, K=1536: 17.5 vs 20.5 us;
     // N=32768, K=512: 10.0 vs 13.0 us).
     const bool wide_short = p.m > 64 && tiles128 >= 48 && kb_all <= 48;
-    if (sbest.split != 0 && ((p.m <= 128 && !wide_short) || (p.m > 128 && sbest.us < best.us))) {
+    // Stream-K window (role of PaddingStreamkMatmulKernel): a pair tile 256 x n1 whose tiles, cut into two K slices,
+    // fill 75-100 % of the pairs in ONE round - half the K loop per pair, short fix-up, no second round.  Of the tile
+    // widths that qualify the one filling most pairs wins (ties: the wider).  Measured (profiles/
+    // r01_streamk_aligned_sweep.log, r01c_selector_audit.log): M=256, N=4096, K=7168: 21.9 vs 24.8 us for split-K +
+    // reduce; K=2048: 13.2 vs 18.9 us; 512 x 2112 x 7168: 21.5 vs 23.2; 768 x 1536 x 7168: 21.6 vs 23.6; 1024 x 1024 x
+    // 4096: 16.4 vs 19.3; 1024 x 1536 x 7168 (n1 = 192): 24.9 vs 27.5 plain; 2048 x 576 x 7168 (n1 = 160): 23.0 vs 27.4.
+    uint32_t sk_n1 = 0, sk_items = 0;
+    // ... and only where the plain walk is in trouble: its best tile is narrower than 128 columns (poor L2 intensity)
+    // or leaves more than 40 % of the pairs idle.  With 56-64 plain tiles of 256 x 128 the single pass wins
+    // (256 x 7168 x 2048: 12.1 vs 18.2 us; 512 x 4096 x 7168: 28.0 vs 30.8 us).
+    const bool plain_weak = best.bn < 128 || 5 * best.tiles < 3 * (platform().smCount / best.cta);
+    if (p.m > 128 && kb_all >= 32 && plain_weak) {
+        const uint32_t step = p.layoutTagB == 0 ? 128 : 32;
+        for (uint32_t bn = 256; bn >= 128; bn -= step) {
+            const uint32_t items = 2 * ceil_div(p.m, 256) * ceil_div(p.n, bn);
+            if (items <= pairs && 4 * items >= 3 * pairs && items > sk_items) { sk_items = items; sk_n1 = bn; }
+        }
+    }
+    const bool rule_sk = sk_n1 != 0;
+    const bool rule_reduce = p.m > 128 && tiles256 * 4 <= pairs && split_r >= 2;
+    if (sbest.split != 0 && ((p.m <= 128 && !wide_short) || (p.m > 128 && !rule_sk && !rule_reduce && sbest.us < best.us))) {
         p.kernelSerial = DGA_KERNEL_SPLITK;
         p.splitkFactor = static_cast<uint16_t>(sbest.split);
         p.stages = static_cast<uint8_t>(sbest.stages);
         p.estTimeUs = sbest.us;
-    } else if (p.m > 128 && p.m <= 256 && 2 * tiles128 <= pairs && 8 * tiles128 >= 3 * pairs && kb_all >= 32) {
-        // Stream-K (role of PaddingStreamkMatmulKernel): one 256-row block, 256 x 128 pair tiles cut into two K
-        // slices fill 75-100 % of the pairs in a single round, and the fix-up of a 128-wide tile is short.  Measured
-        // on B200 (profiles/r01_streamk_aligned_sweep.log), M=256 / 192: N=4096, K=7168: 21.9 / 21.7 us vs 24.8 /
-        // 23.0 for split-K + reduce; N=4096, K=2048: 13.2 / 13.1 vs 18.9 / 17.3 us.  Outside that window (N=2048 or
-        // N=7168) it loses, and so does every shape with more than one 256-row block.
+    } else if (rule_sk) {
         p.kernelSerial = DGA_KERNEL_STREAMK;
         p.ctaGroup = 2;
-        p.n1 = 128;
+        p.n1 = static_cast<uint16_t>(sk_n1);
         p.stages = 0;
         p.splitkFactor = 2;
         p.estTimeUs = best.us;

@@ -21,6 +21,8 @@ def same(plan, cand):
     if plan["kernelSerial"] == 4:
         return cand["kernelSerial"] == 4 and cand.get("ctaGroup") == plan["ctaGroup"] and cand.get("n1") == plan["n1"] \
             and cand.get("splitkFactor", 0) in (0, plan["splitkFactor"])
+    if plan["kernelSerial"] == 5:
+        return cand["kernelSerial"] == 5 and cand.get("splitkFactor") == plan["splitkFactor"]
     return False
 
 
