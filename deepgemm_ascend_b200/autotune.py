@@ -51,6 +51,13 @@ def candidate_plans(m, n, k, layout_b=1):
             if -(-k // 64) >= 14 * split // 2:
                 out.append({"kernelSerial": KERNEL_SPLITK_REDUCE, "ctaGroup": 2, "n1": 256, "stages": 0,
                             "splitkFactor": split})
+    if m <= 128 and layout_b == 0 and -(-k // 64) >= 56:
+        # no swap-AB decode kernel for row-major mat2: K slices of the persistent kernel instead
+        for cta in (2, 1):
+            for n1 in (256, 128):
+                for split in (2, 4, 8):
+                    out.append({"kernelSerial": KERNEL_SPLITK_REDUCE, "ctaGroup": cta, "n1": n1, "stages": 0,
+                                "splitkFactor": split})
     if m <= 256 and layout_b == 1:
         for split in (1, 2, 4, 8):
             if -(-k // 64) < split:
@@ -173,9 +180,10 @@ class _GpuBench:
     against an fp32 torch matmul of the same inputs (a tool-side check, not a product path)."""
     _cache = {}
 
-    def _buffers(self, shape):
+    def _buffers(self, shape, layout_b=1):
         import torch
-        if shape not in self._cache:
+        key = (shape, layout_b)
+        if key not in self._cache:
             self._cache.clear()
             m, n, k = shape
             dev = "cuda:0"
@@ -183,36 +191,39 @@ class _GpuBench:
             sets = max(2, min(16, int(2 * (126 << 20) / nbytes) + 2))
             gen = torch.Generator(device=dev).manual_seed(0)
             a = [torch.rand((m, k), device=dev, generator=gen).add_(0.5).to(torch.bfloat16) for _ in range(sets)]
+            # layout_b 1: weight stored [N, K], mat2 is its transposed view (the aclnn operator's layout);
+            # layout_b 0: mat2 row-major [K, N] (the framework functions' layout)
             w = [torch.rand((n, k), device=dev, generator=gen).add_(0.5).to(torch.bfloat16) for _ in range(sets)]
+            w = [x.t() if layout_b == 1 else x.t().contiguous() for x in w]
             c = [torch.empty((m, n), device=dev, dtype=torch.bfloat16) for _ in range(sets)]
-            self._cache[shape] = (a, w, c)
-        return self._cache[shape]
+            self._cache[key] = (a, w, c)
+        return self._cache[key]
 
     def diff(self, shape, params, layout_b):
         import torch
         from .ops import matmul_with_plan
-        a, w, c = self._buffers(shape)
+        a, w, c = self._buffers(shape, layout_b)
         c[0].zero_()
-        matmul_with_plan(a[0], w[0].t(), c[0], **params)
+        matmul_with_plan(a[0], w[0], c[0], **params)
         torch.cuda.synchronize()
         rows = torch.linspace(0, shape[0] - 1, min(shape[0], 32)).long().to(a[0].device)
-        ref = a[0][rows].float() @ w[0].float().t()
+        ref = a[0][rows].float() @ w[0].float()
         return float(((c[0][rows].float() - ref).abs() / ref.abs().clamp_min(1e-6)).max())
 
     def time(self, shape, params, layout_b, per=10, iters=10):
         import torch
         from .ops import matmul_with_plan
-        a, w, c = self._buffers(shape)
+        a, w, c = self._buffers(shape, layout_b)
         sets = len(a)
         side = torch.cuda.Stream()
         with torch.cuda.stream(side):
             for i in range(min(sets, 3)):
-                matmul_with_plan(a[i], w[i].t(), c[i], **params)
+                matmul_with_plan(a[i], w[i], c[i], **params)
             side.synchronize()
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=side):
                 for i in range(per):
-                    matmul_with_plan(a[i % sets], w[i % sets].t(), c[i % sets], **params)
+                    matmul_with_plan(a[i % sets], w[i % sets], c[i % sets], **params)
         graph.replay()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -1396,9 +1396,6 @@ static aclnnStatus framework_gemm(const void* x, const void* y, void* z, uint32_
     if (rc != ACLNN_SUCCESS) return rc;
     L.a = x; L.b = y; L.d = z;
     L.lda = k; L.ldb = n; L.ldd = n;
-    // stream-K keeps arrival counters in a caller-owned workspace across launches; with scratch that comes and
-    // goes per call (below) a tuned-table row asking for it falls back to the plain persistent walk
-    if (L.plan.kernelSerial == DGA_KERNEL_STREAMK) L.plan.kernelSerial = DGA_KERNEL_COMMON;
     rc = apply_padding(L);   // the reference's kernel takes any (m, n, k): odd n or k go through a repack
     if (rc != ACLNN_SUCCESS) return rc;
     // the framework entry points have no workspace argument (python_api.cpp:13-35): stream-ordered scratch

@@ -383,7 +383,12 @@ int select_kernel(DgaTilingPlan& p) {
     // ... and only where the plain walk is in trouble: its best tile is narrower than 128 columns (poor L2 intensity)
     // or leaves more than 40 % of the pairs idle.  With 56-64 plain tiles of 256 x 128 the single pass wins
     // (256 x 7168 x 2048: 12.1 vs 18.2 us; 512 x 4096 x 7168: 28.0 vs 30.8 us).
-    const bool plain_weak = best.bn < 128 || 5 * best.tiles < 3 * (platform().smCount / best.cta);
+    // Row-major B (the framework layout) is loaded in 64 x 64 boxes and a 256 x 128 tile is much slower there than
+    // with a [N, K] weight (512 x 4096 x 7168: 35.2 us plain vs 30.6 us stream-K on 256 x 256 tiles), so anything
+    // narrower than 256 counts as weak once K >= 4096 (at K = 2048 the single pass still wins: 256 x 7168 x 2048: 13.3
+    // vs 18.4 us).
+    const bool plain_weak = best.bn < ((p.layoutTagB == 0 && kb_all >= 64) ? 256u : 128u) ||
+                            5 * best.tiles < 3 * (platform().smCount / best.cta);
     if (p.m > 128 && kb_all >= 32 && plain_weak) {
         const uint32_t step = p.layoutTagB == 0 ? 128 : 32;
         for (uint32_t bn = 256; bn >= 128; bn -= step) {
@@ -392,8 +397,22 @@ int select_kernel(DgaTilingPlan& p) {
         }
     }
     const bool rule_sk = sk_n1 != 0;
-    const bool rule_reduce = p.m > 128 && tiles256 * 4 <= pairs && split_r >= 2;
-    if (sbest.split != 0 && ((p.m <= 128 && !wide_short) || (p.m > 128 && !rule_sk && !rule_reduce && sbest.us < best.us))) {
+    // (with only 2-3 slices the second launch costs more than the split saves: 256 x 2048 x 2048: 15.6 vs 11.5 us)
+    const bool rule_reduce = p.m > 128 && tiles256 * 4 <= pairs && split_r >= 4;
+    // Row-major mat2 (the framework functions' layout) has no swap-AB decode kernel; up to 128 rows and long K the
+    // weight is streamed by K slices of 128 x 128 single-CTA tiles + the reduce kernel instead, as many slices as
+    // keep the grid within the SM count (audit, profiles/r01c_selector_audit.log: 16 x 4096 x 7168: 15.6 vs 31.6 us
+    // plain; 16 x 2112 x 7168: 11.4 vs 31.2; 128 x 7168 x 16384: 49.6 vs 69.2).
+    const uint32_t sms = platform().smCount;
+    const bool rowmajor_small = p.layoutTagB == 0 && p.m <= 128 && in_b == 2 && kb_all >= 56 && 2 * tiles128 <= sms;
+    if (rowmajor_small) {
+        p.kernelSerial = DGA_KERNEL_SPLITK_REDUCE;
+        p.ctaGroup = 1;
+        p.n1 = 128;
+        p.stages = 0;
+        p.splitkFactor = static_cast<uint16_t>(8 * tiles128 <= sms ? 8 : (4 * tiles128 <= sms ? 4 : 2));
+        p.estTimeUs = best.us;
+    } else if (sbest.split != 0 && ((p.m <= 128 && !wide_short) || (p.m > 128 && !rule_sk && !rule_reduce && sbest.us < best.us))) {
         p.kernelSerial = DGA_KERNEL_SPLITK;
         p.splitkFactor = static_cast<uint16_t>(sbest.split);
         p.stages = static_cast<uint8_t>(sbest.stages);
@@ -405,7 +424,7 @@ int select_kernel(DgaTilingPlan& p) {
         p.stages = 0;
         p.splitkFactor = 2;
         p.estTimeUs = best.us;
-    } else if (p.m > 128 && tiles256 * 4 <= pairs && split_r >= 2) {
+    } else if (rule_reduce) {
         p.kernelSerial = DGA_KERNEL_SPLITK_REDUCE;
         p.ctaGroup = 2;
         p.n1 = 256;

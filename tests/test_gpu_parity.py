@@ -80,6 +80,9 @@ ACLNN_CASES = [
     (256, 4096, 7168, torch.bfloat16, 1, {}),                # the selector's stream-K window (one 256-row block)
     (192, 4096, 2048, torch.bfloat16, 1, {}),
     (200, 4000, 4096, torch.bfloat16, 0, {}),
+    (16, 2112, 7168, torch.bfloat16, 0, {}),                 # row-major mat2, few rows, long K: K slices + reduce kernel
+    (128, 4096, 7168, torch.bfloat16, 0, {}),
+    (512, 4096, 7168, torch.bfloat16, 0, {}),                # row-major mat2: stream-K on 256 x 256 tiles
     (2048, 4096, 2048, torch.bfloat16, 1, {}),
     # stream-K variant (role of PaddingStreamkMatmulKernel): K blocks of the ragged wave dealt out to every cluster
     (512, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 4, "ctaGroup": 2, "n1": 256}),
@@ -358,6 +361,24 @@ def test_framework_path_odd_shapes(dga):
         ok, ratio = orc.verify_result(z.cpu().numpy(), golden, rtol=orc.RTOL_TEST)
         assert ok, ((m, n, k), ratio)
         assert orc.max_rel_err(z.cpu().numpy(), orc.golden_fp64(x1, x2)) < 1e-5
+
+
+def test_framework_path_long_k_variants(dga):
+    """The framework layout (row-major mat2, fp32 out) through the variants the selector gives it for long K: K slices
+    + reduce kernel for few rows, stream-K for one ragged round; scratch workspace comes from the stream-ordered pool.
+    Same comparator as the reference's tests plus the fp64 bound."""
+    for m, n, k in ((64, 512, 4096), (16, 2112, 7168), (512, 4096, 4096)):
+        x1, x2, golden = orc.gen_golden_data(m, n, k, np.random.RandomState(m + n + k))
+        z = torch.zeros((m, n), dtype=torch.float32, device=DEV)
+        params = torch.tensor([1, 1, 4, 4, 8, 4] + [0] * 22, dtype=torch.int32, device=DEV)
+        before = dga.kernel_launch_count()
+        dga.run_mmad_bench(torch.from_numpy(x1).to(DEV), torch.from_numpy(x2).to(DEV), z, params)
+        assert dga.kernel_launch_count() > before
+        ok, ratio = orc.verify_result(z.cpu().numpy(), golden, rtol=orc.RTOL_TEST)
+        assert ok, ((m, n, k), ratio)
+        # fp32 accumulation over 4096-7168 products: the bound grows with K (1e-5 holds up to K ~ 1024 above)
+        err = orc.max_rel_err(z.cpu().numpy(), orc.golden_fp64(x1, x2))
+        assert err < 5e-5, ((m, n, k), err)
 
 
 # ---- batched framework launch and the M-grouped contiguous matmul (SURVEY 8(f) f4) ------------------------------------

@@ -22,7 +22,8 @@ def same(plan, cand):
         return cand["kernelSerial"] == 4 and cand.get("ctaGroup") == plan["ctaGroup"] and cand.get("n1") == plan["n1"] \
             and cand.get("splitkFactor", 0) in (0, plan["splitkFactor"])
     if plan["kernelSerial"] == 5:
-        return cand["kernelSerial"] == 5 and cand.get("splitkFactor") == plan["splitkFactor"]
+        return cand["kernelSerial"] == 5 and cand.get("splitkFactor") == plan["splitkFactor"] and \
+            cand.get("ctaGroup") == plan["ctaGroup"] and cand.get("n1") == plan["n1"]
     return False
 
 
@@ -34,7 +35,7 @@ def main():
         if not recs:
             continue
         m, n, k = recs[0]["M"], recs[0]["N"], recs[0]["K"]
-        plan = dga.select_kernel(m, n, k)
+        plan = dga.select_kernel(m, n, k, layout_b=int(os.environ.get("LAYOUT_B", "1")))
         best = min(recs, key=lambda r: r["time"])
         mine = [r for r in recs if same(plan, r["parameters"])]
         t_mine = min(r["time"] for r in mine) if mine else float("nan")
