@@ -501,3 +501,31 @@ def test_fuzz_against_fp64_oracle(dga, m, n, k, dtype, layout_b, plan):
     got = _run_aclnn(dga, a, b, dtype, layout_b, **plan)
     err = orc.max_rel_err(got, orc.golden_fp64(a, b))
     assert err <= (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7), "max rel err %.3e" % err
+
+
+# ---- second fuzz: the selector's own plan on long-K shapes, where its measured rules (stream-K windows, K slices +
+# reduce kernel, decode kernel, single-CTA tiles) switch from one variant to the next ---------------------------------
+def _selector_fuzz_cases(count=32, seed=4096):
+    rng = np.random.RandomState(seed)
+    cases = []
+    for _ in range(count):
+        m = int(rng.choice([1, 16, 60, 64, 65, 128, 129, 192, 250, 256, 257, 384, 500, 512, 768]))
+        n = int(rng.choice([512, 576, 1000, 1024, 1536, 2048, 2112, 3000, 4096, 4104]))
+        k = int(rng.choice([2048, 2304, 3584, 4096, 5000, 7168, 8192]))
+        layout_b = int(rng.rand() < 0.6)
+        if layout_b == 0:
+            n = (n + 7) // 8 * 8      # keep the row-major pitch 16-byte aligned half of the time
+            if rng.rand() < 0.3:
+                n += 1                # ... and exercise the repack path on the rest
+        cases.append((m, n, k, layout_b))
+    return cases
+
+
+@pytest.mark.parametrize("m,n,k,layout_b", _selector_fuzz_cases())
+def test_selector_plan_fuzz_long_k(dga, m, n, k, layout_b):
+    a, b = _inputs(m, n, k, torch.bfloat16, seed=m + 3 * n + 5 * k)
+    got = _run_aclnn(dga, a, b, torch.bfloat16, layout_b)
+    err = orc.max_rel_err(got, orc.golden_fp64(a, b))
+    assert err <= 2.0 ** -7, "max rel err %.3e with plan %s" % (
+        err, {key: val for key, val in dga.select_kernel(m, n, k, layout_b=layout_b).items()
+              if key in ("kernelSerial", "ctaGroup", "n1", "splitkFactor", "paddingTagB", "paddingTagC")})
