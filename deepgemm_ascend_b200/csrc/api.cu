@@ -215,6 +215,8 @@ static jit::Request make_jit_request(const DgaTilingPlan& p, int mode, uint32_t 
     r.raster_group = gp.raster_group; r.raster_along_m = gp.raster_along_m;
     r.idesc = gp.idesc; r.b_stage_bytes = gp.b_stage_bytes; r.k_block_elems = gp.k_block_elems;
     r.dp_tiles = gp.dp_tiles; r.epi_cols = gp.epi_cols; r.tiles_per_batch = gp.tiles_per_batch;
+    r.split_k = mode == kModeSplitK ? gp.split_k : 1;
+    if (mode == kModeSplitK) r.out_dtype = ACL_FLOAT;   // the slices leave fp32 partial tiles whatever C's type is
     return r;
 }
 
@@ -261,7 +263,7 @@ static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaSt
         // a stream-K plan whose remainder came out empty is the plain walk
         if (gp.sk_tiles != 0) return launch_common_inst<kCta, OutT, kBMn, kMode, true>(L, gp, stream);
     }
-    if constexpr ((kMode == kModePlain || kMode == kModeBatched) && !kSk) {
+    if constexpr ((kMode == kModePlain || kMode == kModeBatched || kMode == kModeSplitK) && !kSk) {
         if (jit_enabled() && L.num_peers == 0) return launch_jit(L, gp, stream, kMode);
     }
     auto kernel = gemm_sm100_kernel<kCta, OutT, kBMn, false, kMode, kSk>;
@@ -1579,8 +1581,9 @@ aclnnStatus dgaJitPrepare(uint32_t batch, uint32_t m, uint32_t n, uint32_t k, in
         if (rc == ACLNN_SUCCESS && plan.kernelSerial == DGA_KERNEL_STREAMK) plan.kernelSerial = DGA_KERNEL_COMMON;
     }
     if (rc != ACLNN_SUCCESS) return rc;
+    if (plan.kernelSerial == DGA_KERNEL_SPLITK_REDUCE && mode == kModePlain) mode = kModeSplitK;
     if (plan.kernelSerial != DGA_KERNEL_COMMON && plan.kernelSerial != DGA_KERNEL_PADDING_COMMON &&
-        plan.kernelSerial != DGA_KERNEL_SMALL) {
+        plan.kernelSerial != DGA_KERNEL_SMALL && plan.kernelSerial != DGA_KERNEL_SPLITK_REDUCE) {
         set_error("the plan for this shape uses a variant that is not specialised at run time (kernelSerial " +
                   std::to_string(int(plan.kernelSerial)) + ")");
         return ACLNN_ERR_PARAM_INVALID;
@@ -1590,6 +1593,11 @@ aclnnStatus dgaJitPrepare(uint32_t batch, uint32_t m, uint32_t n, uint32_t k, in
     if (mode == kModeBatched) {
         gp.tiles_per_batch = gp.dp_tiles;
         gp.dp_tiles *= batch;
+    }
+    if (mode == kModeSplitK) {   // as launch_common sets it up
+        gp.split_k = plan.splitkFactor;
+        gp.dp_tiles *= plan.splitkFactor;
+        gp.epi_cols = 32;
     }
     const jit::Request req = make_jit_request(plan, mode, batch, gp);
     std::string dir, err;

@@ -154,12 +154,12 @@ bool compile(const std::string& dir, const std::string& code, std::string* err) 
 
 std::string signature(const Request& r) {
     // variant knobs, packed: mode[0,2) cta-1[2] b_mn[3] out[4,6) in[6] block_n/16[7,12) stages[12,16)
-    // raster_group[16,24) raster_along_m[24]
+    // raster_group[16,24) raster_along_m[24] split_k[25,30)
     const uint32_t out_code = r.out_dtype == 0 ? 2u : (r.out_dtype == 1 ? 1u : 0u);
     const uint32_t in_code = r.in_dtype == 1 ? 1u : 0u;
     const uint32_t type = (uint32_t(r.mode) & 3u) | ((r.cta - 1u) & 1u) << 2 | (r.b_mn ? 1u : 0u) << 3 | out_code << 4 |
                           in_code << 6 | ((r.block_n / 16u) & 31u) << 7 | (r.stages & 15u) << 12 |
-                          (r.raster_group & 255u) << 16 | (r.raster_along_m & 1u) << 24;
+                          (r.raster_group & 255u) << 16 | (r.raster_along_m & 1u) << 24 | (r.split_k & 31u) << 25;
     char buf[128];
     std::snprintf(buf, sizeof(buf), "b%um%un%uk%u_type%u", r.batch, r.m, r.n, r.k, type);
     return buf;
@@ -190,6 +190,7 @@ std::string generate_code(const Request& r) {
     def("DP_TILES", r.dp_tiles);
     def("EPI_COLS", r.epi_cols);
     def("TILES_PER_BATCH", r.tiles_per_batch);
+    def("SPLIT_K", r.split_k);
     const std::string keep = env_or("DGA_JIT_KEEP_RT", "");   // developer knob, see jit_entry.cuh
     if (!keep.empty()) s << "#define DGA_JIT_KEEP_RT " << std::atoi(keep.c_str()) << "\n";
     s << "#define DGA_JIT_CTA " << r.cta << "\n";

@@ -18,10 +18,11 @@ struct Request {
     int32_t in_dtype = 0;        // ACL_FLOAT16 / ACL_BF16 (part of the key; the arithmetic is in idesc)
     int32_t out_dtype = 0;       // ACL_FLOAT / ACL_FLOAT16 / ACL_BF16
     bool b_mn = false;           // B stored [K, N] row-major
-    int mode = 0;                // kModePlain or kModeBatched
+    int mode = 0;                // kModePlain, kModeBatched or kModeSplitK
     uint32_t block_n = 0, stages = 0, k_blocks = 0, m_blocks = 0, n_blocks = 0;
     uint32_t raster_group = 0, raster_along_m = 0, idesc = 0, b_stage_bytes = 0, k_block_elems = 64;
     uint32_t dp_tiles = 0, epi_cols = 32, tiles_per_batch = 0;
+    uint32_t split_k = 1;        // kModeSplitK: K slices per tile
 };
 
 struct Stats {

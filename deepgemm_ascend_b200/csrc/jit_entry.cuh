@@ -13,6 +13,9 @@
 #ifndef DGA_JIT_KEEP_RT
 #define DGA_JIT_KEEP_RT 0
 #endif
+#ifndef DGA_JIT_SPLIT_K
+#define DGA_JIT_SPLIT_K 1u
+#endif
 #ifndef DGA_JIT_M
 #error "generated unit must define the DGA_JIT_* constants before including jit_entry.cuh"
 #endif
@@ -55,7 +58,7 @@ dga_jit_gemm(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ C
     if (!(DGA_JIT_KEEP_RT & 64)) p.idesc = DGA_JIT_IDESC;
     p.sf_n_chunks = 0;
     p.sf_m_chunks = 0;
-    p.split_k = 1;
+    p.split_k = DGA_JIT_SPLIT_K;
     p.group_index = nullptr;
     dga::gemm_sm100_body<DGA_JIT_CTA, DGA_JIT_OUT_T, DGA_JIT_B_MN, false, DGA_JIT_MODE>(tm_a, tm_b, tm_d, tm_sfa, tm_sfb,
                                                                                        peers, p);

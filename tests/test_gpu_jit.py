@@ -27,6 +27,8 @@ def jit_on(dga, tmp_path, monkeypatch):
     (1024, 1024, 1024, torch.float16, 1),    # BASELINE config 1
     (256, 384, 320, torch.float16, 0),       # row-major B
     (1100, 777, 203, torch.bfloat16, 1),     # unaligned pitches: repack + specialised kernel
+    (256, 2048, 7168, torch.bfloat16, 1),    # split-K + reduce: the GEMM half is specialised (8 slices)
+    (16, 2112, 7168, torch.bfloat16, 0),     # row-major mat2, few rows: K slices of single-CTA tiles
 ])
 def test_specialised_kernel_matches_oracle(jit_on, m, n, k, dtype, layout_b):
     dga = jit_on
