@@ -31,6 +31,7 @@ static std::atomic<uint64_t> g_launches{0};
 static std::atomic<int64_t> g_opt_splitk_prefetch{-1};
 static std::atomic<int64_t> g_opt_pdl{-1};
 static std::atomic<int64_t> g_opt_splitk_batch{-1};
+static std::atomic<int64_t> g_opt_splitk_late{-1};
 static std::atomic<int64_t> g_opt_raster{-1};   // raster_group override (sweeps)
 static std::atomic<int64_t> g_opt_jit{-1};      // shape-specialised kernels compiled at run time (default: $DGA_JIT)
 static bool jit_enabled() {
@@ -520,6 +521,8 @@ static int launch_splitk(DenseLaunch& L, cudaStream_t stream) {
     sp.prefetch_kb = pf >= 0 ? uint32_t(pf) : 4u;
     const int64_t ib = g_opt_splitk_batch.load(std::memory_order_relaxed);
     sp.issue_batch = std::max<uint32_t>(1u, std::min<uint32_t>(ib > 0 ? uint32_t(ib) : 1u, p.stages));
+    const int64_t lt = g_opt_splitk_late.load(std::memory_order_relaxed);
+    sp.late_trigger = lt >= 0 ? uint32_t(std::min<int64_t>(lt, 2)) : 0u;
     sp.out = L.eff.d;
     static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
     sp.trace = (dbg & 16) && L.plan.blockDim * 12 <= kTraceWords ? trace_buffer() : nullptr;
@@ -1554,6 +1557,7 @@ aclnnStatus dgaSetOption(const char* name, int64_t value) {
     if (std::strcmp(name, "splitk_prefetch_kb") == 0) g_opt_splitk_prefetch.store(value);
     else if (std::strcmp(name, "pdl") == 0) g_opt_pdl.store(value);
     else if (std::strcmp(name, "splitk_issue_batch") == 0) g_opt_splitk_batch.store(value);
+    else if (std::strcmp(name, "splitk_late_trigger") == 0) g_opt_splitk_late.store(value);
     else if (std::strcmp(name, "raster_group") == 0) g_opt_raster.store(value);
     else if (std::strcmp(name, "jit") == 0) g_opt_jit.store(value);
     else {

@@ -33,6 +33,9 @@ struct SmallMParams {
     uint32_t issue_batch; // K blocks whose loads the producer issues back to back (<= num_stages)
     unsigned long long* trace; // debug: per CTA 12 words (see tools/trace_smallm.py); nullptr = off
     uint32_t prefetch_kb; // K blocks of this CTA's weight slice pulled into L2 before the grid-dependency wait
+    uint32_t late_trigger; // 0: the successor grid may become resident at once; 1: only after this CTA's last load has
+                           // been issued; 2: after half of them (so that its L2 prefetch fills this grid's reduction
+                           // tail instead of competing with its stream)
     void* out;
 };
 
@@ -69,7 +72,7 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
-    ptx::grid_dep_launch();
+    if (p.late_trigger == 0) ptx::grid_dep_launch();
     unsigned long long* tr = p.trace != nullptr ? p.trace + blockIdx.x * 12 : nullptr;
     if (tr != nullptr && threadIdx.x == 0) { tr[0] = ptx::globaltimer(); tr[2] = clock64(); }
 
@@ -132,6 +135,8 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
             // consecutive K blocks then reach the memory controller together (longer runs per DRAM page).
             uint32_t stage = 0, phase = 0;
             const uint32_t batch = p.issue_batch;
+            const uint32_t trigger_at = p.late_trigger == 1 ? kb1 : (kb0 + kb1 + 1) / 2;
+            bool fired = p.late_trigger == 0;
             for (uint32_t kb = kb0; kb < kb1;) {
                 const uint32_t nb = min(batch, kb1 - kb);
                 uint32_t s2 = stage, ph2 = phase;
@@ -149,6 +154,7 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
                     ptx::mbar_arrive_expect_tx(&full_bar[stage], L.stage_bytes);
                     if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
+                if (!fired && kb >= trigger_at) { ptx::grid_dep_launch(); fired = true; }
             }
         }
         __syncwarp();

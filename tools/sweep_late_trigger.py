@@ -1,0 +1,59 @@
+#!/usr/bin/env python3
+"""Decode kernel: where the programmatic-launch trigger sits (splitk_late_trigger 0 = top of the kernel, 1 = after the
+CTA's last load was issued, 2 = after half of them) x L2 prefetch depth x ring depth, same timing method as
+sweep_smallm.py (CUDA graph of 20 launches, weights rotating beyond L2).  Two passes per point, alternating, best kept."""
+import itertools
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import deepgemm_ascend_b200 as dga  # noqa: E402
+from sweep_smallm import time_point  # noqa: E402
+
+
+def check(m, n, k):
+    import torch
+    a = torch.randn((m, k), device="cuda:0", dtype=torch.bfloat16)
+    w = torch.randn((n, k), device="cuda:0", dtype=torch.bfloat16)
+    ref = a.float() @ w.float().t()
+    for late in (0, 1, 2):
+        dga.set_option("splitk_late_trigger", late)
+        c = torch.empty((m, n), device="cuda:0", dtype=torch.bfloat16)
+        for _ in range(3):   # back to back: the second and third launch depend on the trigger of the one before
+            dga.matmul_with_plan(a, w.t(), c, kernelSerial=3, splitkFactor=8, stages=3)
+        torch.cuda.synchronize()
+        err = ((c.float() - ref).abs().max() / ref.abs().max()).item()
+        print("check m=%d late=%d: max|d|/max|ref| = %.3g" % (m, late, err), flush=True)
+        assert err < 1e-2
+
+
+def main():
+    n, k = 4096, 7168
+    check(1, n, k)
+    check(64, n, k)
+    ms = [int(v) for v in (sys.argv[1].split(",") if len(sys.argv) > 1 else "1,16,64,128".split(","))]
+    for m in ms:
+        plans = {1: [(8, 4), (8, 3)], 16: [(8, 4), (8, 3)], 64: [(8, 3), (8, 2)], 128: [(4, 5), (4, 3)]}[m]
+        pts = list(itertools.product(plans, (0, 1, 2), (4, 8, 32)))
+        res = {}
+        for rep in range(2):
+            for (split, st), late, pf in pts:
+                dga.set_option("splitk_late_trigger", late)
+                dga.set_option("splitk_prefetch_kb", pf)
+                try:
+                    us, gbs = time_point(m, n, k, dict(kernelSerial=3, splitkFactor=split, stages=st), iters=40)
+                except Exception as e:
+                    print("m=%d split=%d stages=%d: %s" % (m, split, st, str(e)[:80]))
+                    continue
+                key = (split, st, late, pf)
+                if key not in res or us < res[key][0]:
+                    res[key] = (us, gbs)
+        for key in sorted(res):
+            print("m=%d split=%d stages=%d late=%d pf=%d: %.2f us %.0f GB/s" % ((m,) + key + res[key]), flush=True)
+        best = min(res, key=lambda q: res[q][0])
+        print("BEST m=%d: split=%d stages=%d late=%d pf=%d %.2f us %.0f GB/s" % ((m,) + best + res[best]), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -47,9 +47,12 @@ def time_point(m, n, k, fields, per=20, iters=60):
 def main():
     n, k = 4096, 7168
     ms = [int(v) for v in (sys.argv[1].split(",") if len(sys.argv) > 1 else "1,16,64,128".split(","))]
+    # optional: comma lists of split factors (any cluster size up to 8, not only powers of two), ring depths, prefetch depths
+    arg = lambda i, d: tuple(int(v) for v in sys.argv[i].split(",")) if len(sys.argv) > i else d
+    splits, depths, pfs = arg(2, (4, 8)), arg(3, (3, 4, 6, 0)), arg(4, (0, 4, 8, 16, 64))
     for m in ms:
         best = None
-        for split, st, pf, pdl in itertools.product((4, 8), (3, 4, 6, 0), (0, 4, 8, 16, 64), (1,)):
+        for split, st, pf, pdl in itertools.product(splits, depths, pfs, (1,)):
             dga.set_option("pdl", pdl)
             dga.set_option("splitk_prefetch_kb", pf)
             try:
