@@ -17,28 +17,35 @@ def check(m, n, k):
     a = torch.randn((m, k), device="cuda:0", dtype=torch.bfloat16)
     w = torch.randn((n, k), device="cuda:0", dtype=torch.bfloat16)
     ref = a.float() @ w.float().t()
-    for late in (0, 1, 2):
+    for late, threads in ((0, 256), (1, 256), (2, 256), (0, 192), (1, 192)):
         dga.set_option("splitk_late_trigger", late)
+        dga.set_option("splitk_threads", threads)
         c = torch.empty((m, n), device="cuda:0", dtype=torch.bfloat16)
         for _ in range(3):   # back to back: the second and third launch depend on the trigger of the one before
             dga.matmul_with_plan(a, w.t(), c, kernelSerial=3, splitkFactor=8, stages=3)
         torch.cuda.synchronize()
         err = ((c.float() - ref).abs().max() / ref.abs().max()).item()
-        print("check m=%d late=%d: max|d|/max|ref| = %.3g" % (m, late, err), flush=True)
+        print("check m=%d n=%d k=%d late=%d threads=%d: max|d|/max|ref| = %.3g" % (m, n, k, late, threads, err), flush=True)
         assert err < 1e-2
+    dga.set_option("splitk_threads", -1)
 
 
 def main():
     n, k = 4096, 7168
     check(1, n, k)
     check(64, n, k)
+    check(128, 1000, 1992)
+    check(50, 520, 4096)
     ms = [int(v) for v in (sys.argv[1].split(",") if len(sys.argv) > 1 else "1,16,64,128".split(","))]
     for m in ms:
-        plans = {1: [(8, 4), (8, 3)], 16: [(8, 4), (8, 3)], 64: [(8, 3), (8, 2)], 128: [(4, 5), (4, 3)]}[m]
-        pts = list(itertools.product(plans, (0, 1, 2), (4, 8, 32)))
+        # (split, ring depth, threads per CTA): 192-thread CTAs fit three to an SM when the ring has <= 3 stages (M <= 16)
+        plans = {1: [(8, 4, 256), (8, 3, 256), (8, 3, 192), (8, 4, 192)], 16: [(8, 4, 256), (8, 3, 256), (8, 3, 192), (8, 4, 192)],
+                 64: [(8, 3, 256), (8, 3, 192)], 128: [(4, 5, 256), (4, 5, 192)]}[m]
+        pts = list(itertools.product(plans, (0, 1), (4, 8, 14)))
         res = {}
         for rep in range(2):
-            for (split, st), late, pf in pts:
+            for (split, st, threads), late, pf in pts:
+                dga.set_option("splitk_threads", threads)
                 dga.set_option("splitk_late_trigger", late)
                 dga.set_option("splitk_prefetch_kb", pf)
                 try:
@@ -46,13 +53,13 @@ def main():
                 except Exception as e:
                     print("m=%d split=%d stages=%d: %s" % (m, split, st, str(e)[:80]))
                     continue
-                key = (split, st, late, pf)
+                key = (split, st, threads, late, pf)
                 if key not in res or us < res[key][0]:
                     res[key] = (us, gbs)
         for key in sorted(res):
-            print("m=%d split=%d stages=%d late=%d pf=%d: %.2f us %.0f GB/s" % ((m,) + key + res[key]), flush=True)
+            print("m=%d split=%d stages=%d threads=%d late=%d pf=%d: %.2f us %.0f GB/s" % ((m,) + key + res[key]), flush=True)
         best = min(res, key=lambda q: res[q][0])
-        print("BEST m=%d: split=%d stages=%d late=%d pf=%d %.2f us %.0f GB/s" % ((m,) + best + res[best]), flush=True)
+        print("BEST m=%d: split=%d stages=%d threads=%d late=%d pf=%d %.2f us %.0f GB/s" % ((m,) + best + res[best]), flush=True)
 
 
 if __name__ == "__main__":
