@@ -31,9 +31,6 @@ static std::atomic<uint64_t> g_launches{0};
 static std::atomic<int64_t> g_opt_splitk_prefetch{-1};
 static std::atomic<int64_t> g_opt_pdl{-1};
 static std::atomic<int64_t> g_opt_splitk_batch{-1};
-static std::atomic<int64_t> g_opt_splitk_late{-1};
-static std::atomic<int64_t> g_opt_splitk_threads{-1};
-static std::atomic<int64_t> g_opt_splitk_fast{-1};
 static std::atomic<int64_t> g_opt_raster{-1};   // raster_group override (sweeps)
 static std::atomic<int64_t> g_opt_jit{-1};      // shape-specialised kernels compiled at run time (default: $DGA_JIT)
 static bool jit_enabled() {
@@ -478,15 +475,15 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
 }
 
 // ---- small-M swap-AB split-K ---------------------------------------------------------------------------
-template <typename OutT, uint32_t kThreads>
-static int launch_splitk_threads(const DenseLaunch& L, const SmallMParams& sp, cudaStream_t stream) {
-    auto kernel = gemm_smallm_sm100_kernel<OutT, kThreads>;
+template <typename OutT>
+static int launch_splitk_inst(const DenseLaunch& L, const SmallMParams& sp, cudaStream_t stream) {
+    auto kernel = gemm_smallm_sm100_kernel<OutT>;
     int rc = set_smem_attr(kernel, L.plan.smemBytes);
     if (rc != ACLNN_SUCCESS) return rc;
     if (sp.split > 8) DGA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(L.plan.blockDim);
-    cfg.blockDim = dim3(kThreads);
+    cfg.blockDim = dim3(kNumThreads);
     cfg.dynamicSmemBytes = L.plan.smemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
@@ -494,14 +491,6 @@ static int launch_splitk_threads(const DenseLaunch& L, const SmallMParams& sp, c
     DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, sp));
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
-}
-
-template <typename OutT>
-static int launch_splitk_inst(const DenseLaunch& L, const SmallMParams& sp, cudaStream_t stream) {
-    // six-warp CTAs (three per SM) whenever the plan's shared memory lets a third CTA in
-    const int64_t th = g_opt_splitk_threads.load(std::memory_order_relaxed);
-    const bool six = th > 0 ? th == 192 : false;
-    return six ? launch_splitk_threads<OutT, 192>(L, sp, stream) : launch_splitk_threads<OutT, 256>(L, sp, stream);
 }
 
 static int launch_splitk(DenseLaunch& L, cudaStream_t stream) {
@@ -531,10 +520,6 @@ static int launch_splitk(DenseLaunch& L, cudaStream_t stream) {
     sp.prefetch_kb = pf >= 0 ? uint32_t(pf) : 4u;
     const int64_t ib = g_opt_splitk_batch.load(std::memory_order_relaxed);
     sp.issue_batch = std::max<uint32_t>(1u, std::min<uint32_t>(ib > 0 ? uint32_t(ib) : 1u, p.stages));
-    const int64_t lt = g_opt_splitk_late.load(std::memory_order_relaxed);
-    sp.late_trigger = lt >= 0 ? uint32_t(std::min<int64_t>(lt, 2)) : 0u;
-    const int64_t fs = g_opt_splitk_fast.load(std::memory_order_relaxed);
-    sp.fast_start = fs >= 0 ? uint32_t(fs != 0) : 0u;
     sp.out = L.eff.d;
     static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
     sp.trace = (dbg & 16) && L.plan.blockDim * 12 <= kTraceWords ? trace_buffer() : nullptr;
@@ -1569,9 +1554,6 @@ aclnnStatus dgaSetOption(const char* name, int64_t value) {
     if (std::strcmp(name, "splitk_prefetch_kb") == 0) g_opt_splitk_prefetch.store(value);
     else if (std::strcmp(name, "pdl") == 0) g_opt_pdl.store(value);
     else if (std::strcmp(name, "splitk_issue_batch") == 0) g_opt_splitk_batch.store(value);
-    else if (std::strcmp(name, "splitk_late_trigger") == 0) g_opt_splitk_late.store(value);
-    else if (std::strcmp(name, "splitk_threads") == 0) g_opt_splitk_threads.store(value);
-    else if (std::strcmp(name, "splitk_fast_start") == 0) g_opt_splitk_fast.store(value);
     else if (std::strcmp(name, "raster_group") == 0) g_opt_raster.store(value);
     else if (std::strcmp(name, "jit") == 0) g_opt_jit.store(value);
     else {

@@ -33,12 +33,6 @@ struct SmallMParams {
     uint32_t issue_batch; // K blocks whose loads the producer issues back to back (<= num_stages)
     unsigned long long* trace; // debug: per CTA 12 words (see tools/trace_smallm.py); nullptr = off
     uint32_t prefetch_kb; // K blocks of this CTA's weight slice pulled into L2 before the grid-dependency wait
-    uint32_t fast_start;   // 1: the producer warp initialises the barriers itself and goes straight on to the dependency
-                           // wait and its first loads; TMEM allocation and the CTA-wide rendezvous (~800 clocks)
-                           // then overlap the first HBM round trip instead of preceding it
-    uint32_t late_trigger; // 0: the successor grid may become resident at once; 1: only after this CTA's last load has
-                           // been issued; 2: after half of them (so that its L2 prefetch fills this grid's reduction
-                           // tail instead of competing with its stream)
     void* out;
 };
 
@@ -68,17 +62,14 @@ __device__ __forceinline__ void store_out(OutT* p, float v) {
     else *p = __float2bfloat16_rn(v);
 }
 
-// kThreads = 256: warps 0 producer, 1 MMA issuer, 2 TMEM, 4-7 epilogue; two CTAs per SM (registers).
-// kThreads = 192: the same roles on six warps (2-5 epilogue, warp 2 also owns the TMEM allocation), so that a third
-// CTA fits the register file and the next launch's CTAs can set themselves up beside a running grid.
-template <typename OutT, uint32_t kThreads = kNumThreads>
-__global__ void __launch_bounds__(kThreads, kThreads == 192 ? 3 : 2)
+template <typename OutT>
+__global__ void __launch_bounds__(kNumThreads, 2)
 gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
                          const SmallMParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
-    if (p.late_trigger == 0) ptx::grid_dep_launch();
+    ptx::grid_dep_launch();
     unsigned long long* tr = p.trace != nullptr ? p.trace + blockIdx.x * 12 : nullptr;
     if (tr != nullptr && threadIdx.x == 0) { tr[0] = ptx::globaltimer(); tr[2] = clock64(); }
 
@@ -101,8 +92,17 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     uint64_t* ack_bar = tmem_full_bar + 2;        // one arrival per owner that has received this CTA's partial
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 4);
 
-    const bool fast = p.fast_start != 0;
-    auto init_barriers = [&]() {
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tensormap(&tm_w);
+        ptx::prefetch_tensormap(&tm_x);
+        // Back-to-back launches (decode: one GEMM after another): this grid becomes resident while its
+        // predecessor is still draining, and HBM would sit idle through that tail and through our own first
+        // round trip.  Pull the head of our weight slice into L2 now; the real loads below hit it there.
+        const uint32_t pf = min(p.prefetch_kb, kb1 - kb0);
+        for (uint32_t i = 0; i < pf; ++i)
+            ptx::tma_prefetch_2d(&tm_w, static_cast<int32_t>((kb0 + i) * 64), static_cast<int32_t>(n0));
+    }
+    if (warp == 1 && lane == 0) {
         for (uint32_t s = 0; s < stages; ++s) {
             ptx::mbar_init(&full_bar[s], 1);
             ptx::mbar_init(&empty_bar[s], 1);
@@ -112,32 +112,12 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
         // owners = CTAs that hold at least one activation row
         ptx::mbar_init(ack_bar, min(split, (p.m + (p.m + split - 1) / split - 1) / ((p.m + split - 1) / split)));
         ptx::fence_mbar_init();
-    };
-    if (warp == 0 && lane == 0) {
-        ptx::prefetch_tensormap(&tm_w);
-        ptx::prefetch_tensormap(&tm_x);
-        if (fast) init_barriers();
-        // Back-to-back launches (decode: one GEMM after another): this grid becomes resident while its
-        // predecessor is still draining, and HBM would sit idle through that tail and through our own first
-        // round trip.  Pull the head of our weight slice into L2 now; the real loads below hit it there.
-        const uint32_t pf = min(p.prefetch_kb, kb1 - kb0);
-        for (uint32_t i = 0; i < pf; ++i)
-            ptx::tma_prefetch_2d(&tm_w, static_cast<int32_t>((kb0 + i) * 64), static_cast<int32_t>(n0));
     }
-    if (warp == 1 && lane == 0 && !fast) init_barriers();
     if (warp == 2) ptx::tmem_alloc<1>(tmem_ptr_smem, p.tmem_cols);
     ptx::tc_fence_before();
-    if (!fast) {
-        __syncthreads();
-    } else if (warp == 0) {
-        // the producer neither needs the TMEM address nor waits for it: it only publishes its barriers
-        __syncwarp();
-        ptx::named_bar_arrive(2, kThreads);
-    } else {
-        ptx::named_bar_sync(2, kThreads);
-    }
+    __syncthreads();
     ptx::tc_fence_after();
-    const uint32_t tmem_base = (fast && warp == 0) ? 0u : *tmem_ptr_smem;
+    const uint32_t tmem_base = *tmem_ptr_smem;
     // Peers will write into this CTA's reduction slots and signal its mbarrier: they may only do so once it is known
     // to be running with the barrier initialised (fence_mbar_init above).  Arrive now, wait (phase 1 of the cluster
     // barrier) just before the first remote access, a whole K slice later.
@@ -152,8 +132,6 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
             // consecutive K blocks then reach the memory controller together (longer runs per DRAM page).
             uint32_t stage = 0, phase = 0;
             const uint32_t batch = p.issue_batch;
-            const uint32_t trigger_at = p.late_trigger == 1 ? kb1 : (kb0 + kb1 + 1) / 2;
-            bool fired = p.late_trigger == 0;
             for (uint32_t kb = kb0; kb < kb1;) {
                 const uint32_t nb = min(batch, kb1 - kb);
                 uint32_t s2 = stage, ph2 = phase;
@@ -171,7 +149,6 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
                     ptx::mbar_arrive_expect_tx(&full_bar[stage], L.stage_bytes);
                     if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
-                if (!fired && kb >= trigger_at) { ptx::grid_dep_launch(); fired = true; }
             }
         }
         __syncwarp();
@@ -208,12 +185,12 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
         if (threadIdx.x == 0 && my_rows != 0) ptx::mbar_arrive_expect_tx(red_full_bar, split * my_rows * 512);
     }
     // Partial tile -> registers -> staging tile -> the owners' reduction slots (or straight to C when K is not split).
-    if (warp >= kThreads / 32 - 4) {
-        const uint32_t lane_base = (warp & 3) * 32;   // the TMEM lane quarter a warp may read is fixed by warp % 4
-        const uint32_t row = lane_base + lane;        // weight row inside the tile == TMEM lane
+    if (warp >= 4) {
+        const uint32_t row = threadIdx.x - 128;  // weight row inside the tile == TMEM lane
+        const uint32_t lane_base = (warp & 3) * 32;
         ptx::mbar_wait(tmem_full_bar, 0);
         ptx::tc_fence_after();
-        if (tr != nullptr && row == 0) tr[7] = clock64();
+        if (tr != nullptr && threadIdx.x == 128) tr[7] = clock64();
         const uint32_t taddr = tmem_base + (lane_base << 16);
         const bool n_ok = n0 + row < p.n;
         // tmem_full fired: every MMA, hence every read of the ring, has completed; the ring is the staging tile now
@@ -261,12 +238,12 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
             if (tr != nullptr && threadIdx.x == 0) tr[8] = clock64();
             // tell every source that its staging tile has been read (it may leave); then reduce
             if (threadIdx.x < split) ptx::mbar_arrive_remote(ack_bar, threadIdx.x);
-            // one row per warp x 32 four-column groups at a time; slots are added in CTA order (deterministic)
+            // 8 rows x 32 four-column groups at a time; slots are added in CTA order (deterministic)
             const uint32_t cg = (threadIdx.x & 31) * 4;
             const float* red = reinterpret_cast<const float*>(smem + L.off_red);
             const bool vec_ok = (reinterpret_cast<uintptr_t>(out) % (4 * sizeof(OutT)) == 0) &&
                                 (p.ldc % 4 == 0) && (n0 + 128 <= p.n);
-            for (uint32_t r = threadIdx.x >> 5; r < my_rows; r += kThreads / 32) {
+            for (uint32_t r = threadIdx.x >> 5; r < my_rows; r += 8) {
                 float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
                 for (uint32_t s = 0; s < split; ++s) {
                     const float4 v = *reinterpret_cast<const float4*>(red + (s * rows_per + r) * 128 + cg);

@@ -377,10 +377,6 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
     asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
 }
-// arrive without waiting (whole warp): the other `nthreads - 32` threads rendezvous with bar.sync on the same id
-__device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t nthreads) {
-    asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
-}
 
 }  // namespace ptx
 }  // namespace dga

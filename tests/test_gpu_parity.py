@@ -231,31 +231,6 @@ def test_rtc_batched(dga):
         assert orc.max_rel_err(out[i].cpu().numpy(), ref) < 1e-5
 
 
-@pytest.mark.parametrize("option,value", [("splitk_late_trigger", 1), ("splitk_late_trigger", 2), ("splitk_fast_start", 0),
-                                          ("splitk_fast_start", 1), ("splitk_threads", 192), ("splitk_threads", 256)])
-def test_decode_kernel_knobs_leave_the_result_bit_identical(dga, option, value):
-    """The decode kernel's scheduling knobs (where the programmatic-launch trigger sits, the producer's early start,
-    six-warp CTAs) change when things happen, never what is summed in which order."""
-    for m, n, k, plan in [(1, 4096, 7168, {}), (64, 4096, 7168, {}), (50, 1000, 1992, {"kernelSerial": 3, "splitkFactor": 3}),
-                          (128, 520, 4096, {"kernelSerial": 3, "splitkFactor": 4})]:
-        a, b = _inputs(m, n, k, torch.bfloat16, seed=m + k)
-        base = _run_aclnn(dga, a, b, torch.bfloat16, 1, **plan)
-        assert orc.max_rel_err(base, orc.golden_fp64(a, b)) <= 2.0 ** -7
-        dga.set_option(option, value)
-        try:
-            ta, w = _to_dev(a, torch.bfloat16), _to_dev(b.T, torch.bfloat16)
-            out = torch.empty((m, n), dtype=torch.bfloat16, device=DEV)
-            for _ in range(3):   # back to back: launches 2 and 3 start under their predecessor's trigger
-                if plan:
-                    dga.matmul_with_plan(ta, w.t(), out, **plan)
-                else:
-                    dga.catlass_dynamic_matmul(ta, w.t(), out=out)
-            torch.cuda.synchronize()
-        finally:
-            dga.set_option(option, -1)
-        assert np.array_equal(out.float().cpu().numpy(), base)
-
-
 def test_stream_k_tolerates_a_dirty_workspace_and_graph_replay(dga):
     """The selector's stream-K plan keeps "partial is ready" flags in the caller's workspace; whatever bytes the
     workspace held before (all ones, random, the leftovers of a previous run) the result is the same, and a captured
