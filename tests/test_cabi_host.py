@@ -77,6 +77,14 @@ def test_phase1_validation_matches_reference_rules(dga, capfd):
     assert rc != 0
     # null arguments
     assert dga._lib.lib.aclnnCatlassDynamicMatmulGetWorkspaceSize(None, None, None, None, None) != 0
+    # empty operands (a zero-sized M, N or K): refused with a message, never a zero-sized launch
+    for shp in [((0, 128), (128, 256), (0, 256)), ((64, 128), (128, 0), (64, 0)), ((64, 0), (0, 256), (64, 256))]:
+        (am, ak), (bk, bn), (cm, cn) = shp
+        capfd.readouterr()
+        rc, _ = _phase1(dga, _desc(dga, (am, ak), (max(ak, 1), 1), BF16), _desc(dga, (bk, bn), (1, max(bk, 1)), BF16),
+                        _desc(dga, (cm, cn), (max(cn, 1), 1), BF16))
+        assert rc != 0
+        assert "[DGA] [ERROR]" in capfd.readouterr().err
     # row-major mat2 (framework layout) is accepted too
     rc, _ = _phase1(dga, ok[0], _desc(dga, (128, 256), (256, 1), BF16), ok[2])
     assert rc == 0
