@@ -177,7 +177,9 @@ def run_ours(args, rank, world):
                        "jit": os.environ.get("DGA_JIT", "0") not in ("", "0"),   # shape-specialised kernels
                        "plan": {key: plan.get(key) for key in ("kernelSerial", "ctaGroup", "m1", "n1", "k1", "stages",
                                                                "splitkFactor", "blockDim")}},
-            "ms_per_step_median": per_step[len(per_step) // 2], "ms_per_step_min": per_step[0],
+            # single launches bracketed by their own events (no overlap with the neighbouring launches' prologue and
+            # tail, which the back-to-back timed region above has): an upper bound per launch, not the bench value
+            "ms_per_isolated_step_median": per_step[len(per_step) // 2], "ms_per_isolated_step_min": per_step[0],
             "roofline": roof, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
     if gather is not None:
         line["allgather"] = gather
