@@ -64,6 +64,16 @@ def candidate_plans(m, n, k, layout_b=1):
                 continue
             for stages in (0, 3, 4, 6):
                 out.append({"kernelSerial": KERNEL_SPLITK, "splitkFactor": split, "stages": stages})
+    if m > 128 and layout_b == 1:
+        # widths that are an odd multiple of 16 (whole-tile plans over a K-major weight): appended last so that the
+        # indices of the candidates above, which are checkpoint keys, stay what they were.  Measured 2-3 % ahead of
+        # the best multiple of 32 where they fill the last wave better (profiles/r01d_odd16_tiles.log), so they are
+        # for the tuned table to pick, not for the analytic selector.
+        for cta in (2, 1):
+            for n1 in range(240, 47, -32):
+                if n1 > -(-n // 16) * 16:
+                    continue
+                out.append({"kernelSerial": KERNEL_COMMON, "ctaGroup": cta, "n1": n1, "stages": 0})
     return out
 
 

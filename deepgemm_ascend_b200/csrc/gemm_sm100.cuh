@@ -35,7 +35,7 @@ constexpr uint32_t kMaxStages = 12;
 
 struct GemmParams {
     uint32_t m, n, k;
-    uint32_t block_n;        // cluster-tile N (multiple of 16 * kCta, <= 256)
+    uint32_t block_n;        // cluster-tile N (multiple of 16, <= 256; odd multiples only for whole-tile K-major plans)
     uint32_t num_stages;     // smem ring depth
     uint32_t k_blocks;       // ceil(k / elements-per-128B)
     uint32_t num_m_blocks;   // cluster tiles along M
@@ -547,7 +547,11 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
             // chunks that intersect the matrix (TMA clips a partial last one)
             const uint32_t n_left = p.n - n0;
-            const uint32_t chunks = min(p.block_n, n_left + kEpiCols - 1) / kEpiCols;
+            const uint32_t chunks = (min(p.block_n, n_left) + kEpiCols - 1) / kEpiCols;
+            // A tile whose width is an odd multiple of 16 (whole-tile plans only): its last chunk is moved back by 16
+            // columns, so that every store stays a whole 32-column box inside the tile; the 16 columns it shares
+            // with its predecessor are written twice with the same values.
+            auto chunk_col = [&](uint32_t c) { return min(c * kEpiCols, p.block_n - kEpiCols); };
             ptx::mbar_wait(&tmem_full_bar[as], aphase);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + (lane_base << 16) + as * p.block_n;
@@ -560,10 +564,10 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             if (kMode == kModeSplitK || !kSk || w.kb1 - w.kb0 == p.k_blocks) {
                 for (uint32_t c = 0; c < chunks; ++c) {
                     uint32_t v[32];
-                    ptx::tmem_ld_32x32(taddr + c * kEpiCols, v);
+                    ptx::tmem_ld_32x32(taddr + chunk_col(c), v);
                     ptx::tmem_ld_wait();
                     if (c + 1 == chunks) release_tmem();
-                    store_chunk(v, m0, n0 + c * kEpiCols, c, c + 1 == chunks);
+                    store_chunk(v, m0, n0 + chunk_col(c), c, c + 1 == chunks);
                 }
             } else {
                 // ---- stream-K slice.  Slices 0 .. S-2 of a tile ("givers") leave their fp32 partial in their

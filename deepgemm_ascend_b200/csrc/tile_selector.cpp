@@ -244,7 +244,14 @@ int finalize_plan(DgaTilingPlan& p) {
     } else {
         if (p.ctaGroup != 1 && p.ctaGroup != 2) p.ctaGroup = 2;
         const uint32_t cta = p.ctaGroup;
-        if (p.n1 == 0 || p.n1 > 256 || p.n1 % 32 != 0 || p.n1 % (16 * cta) != 0 || (p.layoutTagB == 0 && (p.n1 / cta) % 64 != 0)) {
+        // widths that are an odd multiple of 16 (240, 208, ...: UMMA N is legal in steps of 16 for both CTA groups, each
+        // CTA of a pair then holds n1 / 2 = whole 8-row swizzle atoms of B): whole-tile plans over a K-major weight
+        // only; the partial-tile slots of stream-K and the wide-row epilogue assume 32-column chunks
+        const bool odd16 = p.n1 % 32 == 16;
+        const bool odd16_ok = p.n1 > 32 && p.layoutTagB == 1 &&
+                              (p.kernelSerial == DGA_KERNEL_COMMON || p.kernelSerial == DGA_KERNEL_SMALL ||
+                               p.kernelSerial == DGA_KERNEL_PADDING_COMMON);
+        if (p.n1 == 0 || p.n1 > 256 || p.n1 % 16 != 0 || (odd16 && !odd16_ok) || (p.layoutTagB == 0 && (p.n1 / cta) % 64 != 0)) {
             set_error("invalid n1 for the persistent kernel: " + std::to_string(p.n1));
             return ACLNN_ERR_INNER_TILING_ERROR;
         }

@@ -198,6 +198,39 @@ def test_selector_decision_structure(dga):
     assert dga.select_kernel(128, 128, 128)["kernelSerial"] in (1, 3)
 
 
+def test_tile_widths_that_are_odd_multiples_of_16(dga):
+    """n1 = 240, 208, ... (UMMA N is legal in steps of 16): accepted for whole-tile plans over a K-major weight, refused
+    for stream-K (its partial-tile slots are cut in 32-column chunks), for row-major mat2 and below 48."""
+    lib = dga._lib.lib
+
+    def try_plan(layout_b=1, **fields):
+        lib.dgaTilingCacheClear()
+        plan = dga._lib.TilingPlan()
+        for key, val in dga.select_kernel(2048, 4096, 7168, layout_b=layout_b).items():
+            setattr(plan, key, val)
+        plan.stages = 0
+        for key, val in fields.items():
+            setattr(plan, key, val)
+        rc = lib.dgaTilingCacheSet(ctypes.byref(plan))
+        got = dga.select_kernel(2048, 4096, 7168, layout_b=layout_b, use_cache=True) if rc == 0 else None
+        lib.dgaTilingCacheClear()
+        return rc, got
+
+    rc, got = try_plan(kernelSerial=0, ctaGroup=2, n1=240)
+    assert rc == 0 and got["n1"] == 240 and got["stages"] >= 4 and got["smemBytes"] <= 232448
+    rc, got = try_plan(kernelSerial=0, ctaGroup=1, n1=208)
+    assert rc == 0 and got["n1"] == 208
+    assert try_plan(kernelSerial=4, ctaGroup=2, n1=240, splitkFactor=2)[0] != 0
+    assert try_plan(kernelSerial=0, ctaGroup=2, n1=16)[0] != 0
+    assert try_plan(kernelSerial=0, ctaGroup=2, n1=40)[0] != 0
+    assert try_plan(layout_b=0, kernelSerial=0, ctaGroup=1, n1=240)[0] != 0
+    # the tuned-table sweep offers them (after every older candidate: indices are checkpoint keys)
+    import deepgemm_ascend_b200.autotune as at
+    cands = at.candidate_plans(2048, 4096, 7168)
+    odd = [i for i, p in enumerate(cands) if p.get("n1", 0) % 32 == 16]
+    assert odd and odd[0] > max(i for i, p in enumerate(cands) if p.get("n1", 0) % 32 == 0 or "n1" not in p)
+
+
 def test_cache_first_writer_wins_and_csv_round_trip(dga, tmp_path):
     lib = dga._lib.lib
     lib.dgaTilingCacheClear()

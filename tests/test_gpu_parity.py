@@ -68,6 +68,12 @@ ACLNN_CASES = [
     (1000, 1000, 1000, torch.bfloat16, 1, {}),
     (1000, 1000, 1000, torch.bfloat16, 1, {"kernelSerial": 0, "ctaGroup": 2, "n1": 224}),
     (512, 1024, 512, torch.float16, 0, {"kernelSerial": 0, "ctaGroup": 1, "n1": 128}),
+    # tile widths that are an odd multiple of 16: the last 32-column store is moved back by 16 columns
+    (2048, 4096, 2048, torch.bfloat16, 1, {"kernelSerial": 0, "ctaGroup": 2, "n1": 240}),
+    (1000, 1000, 1000, torch.bfloat16, 1, {"kernelSerial": 0, "ctaGroup": 2, "n1": 208}),
+    (300, 520, 1992, torch.float16, 1, {"kernelSerial": 0, "ctaGroup": 1, "n1": 240}),
+    (257, 4088, 640, torch.bfloat16, 1, {"kernelSerial": 0, "ctaGroup": 2, "n1": 48}),
+    (127, 509, 1027, torch.bfloat16, 1, {"kernelSerial": 2, "ctaGroup": 1, "n1": 80}),   # + repack of A, B, C
     (1, 512, 128, torch.bfloat16, 1, {}),                    # the reference's own test shape (test.py:24-26)
     (1, 4096, 7168, torch.bfloat16, 1, {}),
     (16, 4096, 7168, torch.bfloat16, 1, {}),
