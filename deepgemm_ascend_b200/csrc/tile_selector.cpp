@@ -337,9 +337,14 @@ int select_kernel(DgaTilingPlan& p) {
         // up to 128 rows a pair tile spends half of its tensor work on rows that do not exist (audit: M=128,
         // N=32768, K=512: 10.0 us single-CTA vs 11.8 us pair; N=24576, K=1536: 17.5 vs 19.8 us)
         if (cta == 2 && p.m <= 128) continue;
-        const uint32_t step = (p.layoutTagB == 0) ? 64 * cta : 16 * cta;
+        const uint32_t step = (p.layoutTagB == 0) ? 64 * cta : 16;
         for (uint32_t bn = 256; bn >= step && bn >= 32; bn -= step) {
-            if (bn % 32 != 0) continue;  // epilogue works in 32-column chunks
+            // Odd multiples of 16 (240, 208, ...) only where they cut N into as many column tiles as the next multiple
+            // of 32: same tiles, same waves, every tile cheaper and fewer bytes through the crossbar (2048 x 2112 x
+            // 7168: 240 vs 256, 44.4 vs 45.5 us; 4096 x 2112 x 7168: 85.5 vs 88.2 us).  Where they add tiles the wave
+            // model over-rates them (2048 x 4096 x 7168: promised 6 %, measured 0.3 %; 1024 x 4096 x 7168: -0.6 %;
+            // profiles/r01d_odd16_tiles.log), so those are left to the tuned table.
+            if (bn % 32 != 0 && (bn < 48 || ceil_div(p.n, bn) != ceil_div(p.n, bn + 16))) continue;
             Cand c = eval_common(p, cta, bn);
             // prefer (on ties within 1 %) the pair mode and the larger tile
             if (c.us < best.us * 0.99) best = c;
@@ -444,7 +449,7 @@ int select_kernel(DgaTilingPlan& p) {
         // (audit: 2048 x 7168 x 16384: 279 vs 326 us; 4096 x 7168 x 16384: 575 vs 601 us; 4096 x 4096 x 7168: 143 vs 147 us).
         const uint32_t clusters = platform().smCount / best.cta;
         const uint32_t full = best.tiles / clusters, rem = best.tiles % clusters;
-        if (best.cta == 2 && full >= 1 && rem != 0 && 2 * rem <= clusters && kb_all >= 64) {
+        if (best.cta == 2 && best.bn % 32 == 0 && full >= 1 && rem != 0 && 2 * rem <= clusters && kb_all >= 64) {
             // two slices per ragged tile, one round: the only configuration the audit shows winning (more slices or
             // a second round and the owners' adding passes eat the gain: 1024 x 7168 x 16384 with 5 slices: 234 vs 148 us)
             const uint32_t cost = streamk_rounds_cost(rem, 2, clusters, kb_all, streamk_overhead_kb(best.bn));

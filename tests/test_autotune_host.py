@@ -83,3 +83,24 @@ def test_two_ranks_then_csv_feeds_the_plan_cache(tmp_path, dga):
     p = dga.select_kernel(4096, 7168, 2048, use_cache=True)
     assert (p["ctaGroup"], p["n1"]) == (2, 224)
     lib.dgaTilingCacheClear()
+
+
+def test_shipped_tuned_table_loads_and_overrides_the_selector(dga):
+    """deepgemm_ascend_b200/tuned/*.csv: every row passes the library's plan validation, and a loaded row wins over
+    the analytic plan for its shape (first writer wins, cache.cpp:69-77)."""
+    import csv
+    import os
+    lib = dga._lib.lib
+    path = os.path.join(os.path.dirname(dga.__file__), "tuned", "b200_deepseek_v3_bf16.csv")
+    rows = list(csv.DictReader(open(path)))
+    assert rows
+    lib.dgaTilingCacheClear()
+    try:
+        assert lib.dgaTilingCacheLoadCsv(path.encode()) == 0
+        assert lib.dgaTilingCacheSize() == len(rows)
+        for r in rows:
+            got = dga.select_kernel(int(r["m"]), int(r["n"]), int(r["k"]), use_cache=True)
+            assert (got["n1"], got["ctaGroup"], got["kernelSerial"]) == (int(r["n1"]), int(r["ctaGroup"]), int(r["kernelSerial"]))
+            assert got["smemBytes"] <= 232448
+    finally:
+        lib.dgaTilingCacheClear()
