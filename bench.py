@@ -25,6 +25,12 @@ import sys
 import threading
 import time
 
+if "reference" in sys.argv[1:]:
+    # torch.distributed.run exports OMP_NUM_THREADS=1 to every rank it starts; the reference arm is the CPU golden
+    # "with all the host threads it can use", so the BLAS pool must be sized before numpy loads it
+    for _var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ.pop(_var, None)
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
