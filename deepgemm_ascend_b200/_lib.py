@@ -31,7 +31,7 @@ class TilingPlan(ctypes.Structure):
                 ("layoutTagA", ctypes.c_uint8), ("layoutTagB", ctypes.c_uint8), ("layoutTagC", ctypes.c_uint8),
                 ("paddingTagA", ctypes.c_uint8), ("paddingTagB", ctypes.c_uint8), ("paddingTagC", ctypes.c_uint8),
                 ("kernelSerial", ctypes.c_uint8), ("ctaGroup", ctypes.c_uint8), ("stages", ctypes.c_uint8),
-                ("dtype", ctypes.c_uint8), ("outDtype", ctypes.c_uint8),
+                ("dtype", ctypes.c_uint8), ("outDtype", ctypes.c_uint8), ("clusterShape", ctypes.c_uint8),
                 ("blockDim", ctypes.c_uint32), ("smemBytes", ctypes.c_uint32),
                 ("workspaceBytes", ctypes.c_uint64), ("estTimeUs", ctypes.c_double)]
 
@@ -60,6 +60,7 @@ SIGNATURES = {
     "dgaDestroyExecutor": (_i32, [_vp]),
     "dgaFp8BlockScaledMatmulGetWorkspaceSize": (_i32, [_P(AclTensor)] * 5 + [_P(_u64), _P(_vp)]),
     "dgaFp8BlockScaledMatmul": (_i32, [_vp, _u64, _vp, _vp]),
+    "dgaFp8QueryPath": (_i32, [_vp, _vp, _vp, _P(_i32)]),
     "dgaSelectKernel": (_i32, [_u32, _u32, _u32, _i32, _i32, _i32, _P(TilingPlan)]),
     "dgaSelectKernelWithCache": (_i32, [_u32, _u32, _u32, _i32, _i32, _i32, _P(TilingPlan)]),
     "dgaTilingCacheSet": (_i32, [_P(TilingPlan)]),

@@ -257,16 +257,20 @@ static int launch_jit(const DenseLaunch& L, const GemmParams& gp, cudaStream_t s
     return ACLNN_SUCCESS;
 }
 
-template <int kCta, typename OutT, bool kBMn, int kMode = kModePlain, bool kSk = false>
+template <int kCta, typename OutT, bool kBMn, int kMode = kModePlain, bool kSk = false, bool kMc = false>
 static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaStream_t stream) {
-    if constexpr (kMode == kModePlain && !kSk) {
+    if constexpr (kMode == kModePlain && !kSk && !kMc) {
         // a stream-K plan whose remainder came out empty is the plain walk
         if (gp.sk_tiles != 0) return launch_common_inst<kCta, OutT, kBMn, kMode, true>(L, gp, stream);
+        // two CTA pairs per cluster, A multicast between them (16-bit outputs over either weight layout)
+        if constexpr (kCta == 2 && sizeof(OutT) == 2) {
+            if (L.plan.clusterShape == 4) return launch_common_inst<kCta, OutT, kBMn, kMode, false, true>(L, gp, stream);
+        }
     }
-    if constexpr ((kMode == kModePlain || kMode == kModeBatched || kMode == kModeSplitK) && !kSk) {
+    if constexpr ((kMode == kModePlain || kMode == kModeBatched || kMode == kModeSplitK) && !kSk && !kMc) {
         if (jit_enabled() && L.num_peers == 0) return launch_jit(L, gp, stream, kMode);
     }
-    auto kernel = gemm_sm100_kernel<kCta, OutT, kBMn, false, kMode, kSk>;
+    auto kernel = gemm_sm100_kernel<kCta, OutT, kBMn, false, kMode, kSk, kMc>;
     int rc = set_smem_attr(kernel, L.plan.smemBytes);
     if (rc != ACLNN_SUCCESS) return rc;
     cudaLaunchConfig_t cfg{};
@@ -275,7 +279,7 @@ static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaSt
     cfg.dynamicSmemBytes = L.plan.smemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
-    fill_launch_attrs(cfg, attr, kCta);
+    fill_launch_attrs(cfg, attr, kMc ? 4 : kCta);
     DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, L.tm_a, L.tm_b, L.peers, gp));  // no scale maps here
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
@@ -330,7 +334,9 @@ static int encode_common(DenseLaunch& L) {
         return make_tmap_3d(&L.tm_b, L.eff.b, p.dtype, p.n, p.k, slabs, L.eff.ldb, L.slab_b, 64, 64,
                             CU_TENSOR_MAP_SWIZZLE_128B);
     }
-    int rc = make_tmap_2d(&L.tm_a, L.eff.a, p.dtype, p.k, p.m, L.eff.lda, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+    // clusterShape 4: every CTA fetches half of its 128 A rows and receives the other half from its twin
+    int rc = make_tmap_2d(&L.tm_a, L.eff.a, p.dtype, p.k, p.m, L.eff.lda, 64, p.clusterShape == 4 ? 64 : 128,
+                          CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != ACLNN_SUCCESS) return rc;
     if (p.layoutTagB == 1)  // weight stored [N, K]
         rc = make_tmap_2d(&L.tm_b, L.eff.b, p.dtype, p.k, p.n, L.eff.ldb, 64, load_n, CU_TENSOR_MAP_SWIZZLE_128B);
@@ -374,6 +380,7 @@ static void common_params(const DgaTilingPlan& p, GemmParams& gp) {
     gp.k_blocks = ceil_div(p.k, 64);
     gp.num_m_blocks = ceil_div(p.m, 128 * cta);
     gp.num_n_blocks = ceil_div(p.n, p.n1);
+    if (p.clusterShape == 4) gp.num_n_blocks /= 2;   // the cluster walks pairs of N tiles (finalize_plan: even count)
     gp.raster_group = p.swizzleOffset;
     if (g_opt_raster.load(std::memory_order_relaxed) > 0) gp.raster_group = uint32_t(g_opt_raster.load());
     gp.raster_along_m = p.swizzleDirection;
@@ -1083,7 +1090,7 @@ aclnnStatus dgaNShardMatmulGetWorkspaceSize(const aclTensor* self, const aclTens
         if (rc == ACLNN_SUCCESS && p.kernelSerial != DGA_KERNEL_COMMON && p.kernelSerial != DGA_KERNEL_SMALL) {
             DgaTilingPlan q{};
             q.m = p.m; q.n = p.n; q.k = p.k; q.dtype = p.dtype; q.outDtype = p.outDtype; q.layoutTagB = p.layoutTagB;
-            q.kernelSerial = DGA_KERNEL_COMMON; q.ctaGroup = 2; q.n1 = p.layoutTagB ? 128 : 128;
+            q.kernelSerial = DGA_KERNEL_COMMON; q.ctaGroup = 2; q.n1 = 128;
             rc = finalize_plan(q);
             if (rc == ACLNN_SUCCESS) { q.strideA = p.strideA; q.strideB = p.strideB; q.strideC = p.strideC; p = q; }
         }
@@ -1182,6 +1189,18 @@ aclnnStatus dgaFp8BlockScaledMatmul(void* workspace, uint64_t workspaceSize, acl
     }
     if (!executor->repeatable) delete executor;
     return rc;
+}
+
+aclnnStatus dgaFp8QueryPath(void* workspace, aclOpExecutor* executor, aclrtStream stream, int32_t* path) {
+    if (workspace == nullptr || executor == nullptr || path == nullptr || !executor->is_fp8) {
+        set_error("dgaFp8QueryPath wants an fp8 executor, its workspace and an output");
+        return ACLNN_ERR_PARAM_NULLPTR;
+    }
+    DGA_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    int32_t flag = -1;
+    DGA_CUDA(cudaMemcpy(&flag, static_cast<char*>(workspace) + executor->fp8.ws_flag_off, sizeof(flag), cudaMemcpyDeviceToHost));
+    *path = flag != 0 ? 1 : 0;
+    return ACLNN_SUCCESS;
 }
 
 // ---- M-grouped contiguous matmul (MoE) -------------------------------------------------------------------------

@@ -269,7 +269,14 @@ __device__ __forceinline__ void resolve_item(const GemmParams& p, WorkItem& w, u
 // field of GemmParams read at run time) and the shape-specialised entry a JIT build wraps around it
 // (jit_entry.cuh: the shape fields are compile-time constants there and fold through the inlined body).
 // The tensor maps must be the kernel's own __grid_constant__ parameters (TMA takes their address).
-template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain, bool kSk = false>
+// kMc (north_star item 1, "TMA multicast loads"; role of the L1 staging + swizzle of CommonMatmulKernel,
+// common_matmul_kernel.h:28-78): a cluster of FOUR CTAs = two cta_group::2 pairs on neighbouring N tiles of one
+// 256-row block.  Both pairs need the same A rows, so each CTA fetches only 64 of its 128 A rows per stage and the
+// load is multicast to the CTA of the same rank in the other pair: a third (n1 = 128) to a quarter (n1 = 256) fewer
+// bytes leave L2 per flop.  A stage may be refilled once BOTH pairs have consumed it: every leader's commit goes
+// to the empty barrier of all four CTAs (count 2).  Everything behind the ring (TMEM, epilogue) stays per pair.
+// num_n_blocks then counts 2 * block_n wide column groups; the host only takes it for an even number of N tiles.
+template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain, bool kSk = false, bool kMc = false>
 __device__ __forceinline__ void
 gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensorMap& tm_d, const CUtensorMap& tm_sfa,
                 const CUtensorMap& tm_sfb, const PeerMaps& peers, const GemmParams& p) {
@@ -278,6 +285,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                   "batched / grouped modes are single-CTA, 16-bit");
     static_assert(kMode != kModeSplitK || (sizeof(OutT) == 4 && !kMx), "split-K slices leave fp32 partial tiles");
     static_assert(!kSk || (kMode == kModePlain && !kMx), "stream-K is a variant of the plain 16-bit kernel");
+    static_assert(!kMc || (kCta == 2 && kMode == kModePlain && !kSk && !kMx), "the multicast cluster is two whole-tile 16-bit CTA pairs");
     ptx::grid_dep_launch();   // the next grid on the stream may set itself up while this one runs
     const bool tracing = (p.debug & 16) != 0 && p.trace != nullptr;
     if (tracing && threadIdx.x == 0) {
@@ -294,10 +302,14 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
 
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t cta_rank = (kCta == 2) ? ptx::cluster_ctarank() : 0u;
+    constexpr uint32_t kClusterCtas = kMc ? 4 : kCta;
+    const uint32_t cluster_rank = (kCta == 2) ? ptx::cluster_ctarank() : 0u;
+    const uint32_t pair = kMc ? cluster_rank >> 1 : 0u;        // which of the cluster's CTA pairs (N neighbour)
+    const uint32_t cta_rank = kMc ? cluster_rank & 1u : cluster_rank;   // rank inside the pair
+    const uint32_t leader_rank = pair * 2;                     // cluster rank of this pair's MMA-issuing CTA
     const bool is_leader = cta_rank == 0;
-    const uint32_t num_clusters = gridDim.x / kCta;
-    const uint32_t cluster_id = blockIdx.x / kCta;
+    const uint32_t num_clusters = gridDim.x / kClusterCtas;
+    const uint32_t cluster_id = blockIdx.x / kClusterCtas;
     const uint32_t stages = p.num_stages;
 
     const uint32_t sf_stage_bytes = kMx ? 512u * (1u + p.sf_n_chunks) : 0u;
@@ -322,7 +334,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
     if (warp == 1 && lane == 0) {
         for (uint32_t s = 0; s < stages; ++s) {
             ptx::mbar_init(&full_bar[s], kCta);  // leader expect_tx arrive (+ peer's remote arrive)
-            ptx::mbar_init(&empty_bar[s], 1);    // one tcgen05.commit (multicast to both CTAs)
+            ptx::mbar_init(&empty_bar[s], kMc ? 2 : 1);   // one tcgen05.commit per pair that reads the stage (multicast)
         }
         for (uint32_t s = 0; s < 2; ++s) {
             ptx::mbar_init(&tmem_full_bar[s], 1);
@@ -351,6 +363,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             resolve_item<kMode>(p, w, slab);
             int32_t z = static_cast<int32_t>(slab);   // third tensor-map coordinate: batch entry (mode 1) or group (mode 2)
             tile_coords(p, w.tile, mb, nb);
+            if constexpr (kMc) nb = nb * 2 + pair;
             const int32_t m_idx = static_cast<int32_t>(mb * (kBlockM * kCta) + cta_rank * kBlockM);
             const int32_t n_idx = static_cast<int32_t>(nb * p.block_n + cta_rank * load_n);
             if constexpr (kMode == kModeMGrouped) {
@@ -365,7 +378,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                 if (p.debug & 1) {
                     if (ptx::elect_one()) {
                         if (is_leader) ptx::mbar_arrive(&full_bar[stage]);
-                        else ptx::mbar_arrive_remote(&full_bar[stage], 0);
+                        else ptx::mbar_arrive_remote(&full_bar[stage], leader_rank);
                     }
                 } else if (ptx::elect_one()) {
                     uint8_t* sa = smem + L.off_a + stage * L.a_stage_bytes;
@@ -391,7 +404,12 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                         }
                     }
                     if constexpr (kCta == 2) {
-                        ptx::tma_load_2d_pair(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
+                        if constexpr (kMc)   // 64 of this CTA's A rows, for itself and for its twin in the other pair
+                            ptx::tma_load_2d_pair_multicast(&tm_a, &full_bar[stage], sa + pair * (kBlockM / 2) * kBlockKBytes,
+                                                            k_idx, m_idx + static_cast<int32_t>(pair * (kBlockM / 2)),
+                                                            static_cast<uint16_t>(0x5u << cta_rank));
+                        else
+                            ptx::tma_load_2d_pair(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
                         if constexpr (kBMn) {
                             for (uint32_t j = 0; j < load_n / 64; ++j)
                                 ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb + j * 8192, n_idx + j * 64, k_idx);
@@ -399,7 +417,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                             ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
                         }
                         if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * (L.a_stage_bytes + L.b_stage_bytes + sf_bytes));
-                        else ptx::mbar_arrive_remote(&full_bar[stage], 0);
+                        else ptx::mbar_arrive_remote(&full_bar[stage], leader_rank);
                     } else {
                         if constexpr (mode_is_batched(kMode)) ptx::tma_load_3d(&tm_a, &full_bar[stage], sa, k_idx, m_idx, z);
                         else ptx::tma_load_2d(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
@@ -485,8 +503,14 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                             else if (!(p.debug & 2))
                                 ptx::mma_f16<kCta>(tmem_d, a_desc, b_desc, idesc_k, ((kb - kb0) | k) != 0);
                         }
-                        ptx::mma_commit<kCta>(&empty_bar[stage]);
-                        if (kb + 1 == k_blocks) ptx::mma_commit<kCta>(&tmem_full_bar[as]);
+                        if constexpr (kMc) {
+                            ptx::mma_commit_multicast<kCta>(&empty_bar[stage], 0xF);
+                            if (kb + 1 == k_blocks)
+                                ptx::mma_commit_multicast<kCta>(&tmem_full_bar[as], static_cast<uint16_t>(0x3u << leader_rank));
+                        } else {
+                            ptx::mma_commit<kCta>(&empty_bar[stage]);
+                            if (kb + 1 == k_blocks) ptx::mma_commit<kCta>(&tmem_full_bar[as]);
+                        }
                     }
                     __syncwarp();
                     if (++stage == stages) { stage = 0; phase ^= 1; }
@@ -536,6 +560,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             resolve_item<kMode>(p, w, slab);
             zb = static_cast<int32_t>(slab);
             tile_coords(p, w.tile, mb, nb);
+            if constexpr (kMc) nb = nb * 2 + pair;
             const uint32_t m0 = mb * (kBlockM * kCta) + cta_rank * kBlockM;
             const uint32_t n0 = nb * p.block_n;
             if constexpr (kMode == kModeMGrouped) {
@@ -558,7 +583,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             auto release_tmem = [&]() {
                 // accumulator fully read: hand the TMEM stage back to the issuer
                 ptx::tc_fence_before();
-                if constexpr (kCta == 2) ptx::mbar_arrive_remote(&tmem_empty_bar[as], 0);
+                if constexpr (kCta == 2) ptx::mbar_arrive_remote(&tmem_empty_bar[as], leader_rank);
                 else ptx::mbar_arrive(&tmem_empty_bar[as]);
             };
             if (kMode == kModeSplitK || !kSk || w.kb1 - w.kb0 == p.k_blocks) {
@@ -685,13 +710,13 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
     }
 }
 
-template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain, bool kSk = false>
+template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain, bool kSk = false, bool kMc = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                   const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_sfa,
                   const __grid_constant__ CUtensorMap tm_sfb, const __grid_constant__ PeerMaps peers,
                   const GemmParams p) {
-    gemm_sm100_body<kCta, OutT, kBMn, kMx, kMode, kSk>(tm_a, tm_b, tm_d, tm_sfa, tm_sfb, peers, p);
+    gemm_sm100_body<kCta, OutT, kBMn, kMx, kMode, kSk, kMc>(tm_a, tm_b, tm_d, tm_sfa, tm_sfb, peers, p);
 }
 
 }  // namespace dga

@@ -21,8 +21,8 @@ using Key = std::tuple<uint32_t, uint32_t, uint32_t, int32_t, int32_t, int32_t>;
 
 const char* kHeader =
     "m,n,k,m1,n1,k1,kernelSerial,paddingTagA,paddingTagB,paddingTagC,blockDim,"
-    "ctaGroup,stages,splitkFactor,swizzleOffset,swizzleDirection,dtype,outDtype,layoutTagB";
-constexpr size_t kRefColumns = 11, kAllColumns = 19;
+    "ctaGroup,stages,splitkFactor,swizzleOffset,swizzleDirection,dtype,outDtype,layoutTagB,clusterShape";
+constexpr size_t kRefColumns = 11, kR1Columns = 19, kAllColumns = 20;   // 19: tables written before clusterShape existed
 
 struct Cache {
     std::mutex mu;
@@ -41,7 +41,8 @@ std::string row_of(const DgaTilingPlan& p) {
     os << p.m << ',' << p.n << ',' << p.k << ',' << p.m1 << ',' << p.n1 << ',' << p.k1 << ',' << int(p.kernelSerial)
        << ',' << int(p.paddingTagA) << ',' << int(p.paddingTagB) << ',' << int(p.paddingTagC) << ',' << p.blockDim
        << ',' << int(p.ctaGroup) << ',' << int(p.stages) << ',' << p.splitkFactor << ',' << int(p.swizzleOffset) << ','
-       << int(p.swizzleDirection) << ',' << int(p.dtype) << ',' << int(p.outDtype) << ',' << int(p.layoutTagB);
+       << int(p.swizzleDirection) << ',' << int(p.dtype) << ',' << int(p.outDtype) << ',' << int(p.layoutTagB) << ','
+       << int(p.clusterShape);
     return os.str();
 }
 
@@ -56,17 +57,19 @@ bool parse_row(const std::string& line, DgaTilingPlan& p) {
         if (end == cell.c_str()) return false;
         v.push_back(x);
     }
-    if (v.size() != kRefColumns && v.size() != kAllColumns) return false;
+    if (v.size() != kRefColumns && v.size() != kR1Columns && v.size() != kAllColumns) return false;
     p = DgaTilingPlan{};
     p.m = uint32_t(v[0]); p.n = uint32_t(v[1]); p.k = uint32_t(v[2]);
     p.m1 = uint16_t(v[3]); p.n1 = uint16_t(v[4]); p.k1 = uint16_t(v[5]);
     p.kernelSerial = uint8_t(v[6]);
     p.paddingTagA = uint8_t(v[7]); p.paddingTagB = uint8_t(v[8]); p.paddingTagC = uint8_t(v[9]);
     p.blockDim = uint32_t(v[10]);
-    if (v.size() == kAllColumns) {
+    if (v.size() >= kR1Columns) {
         p.ctaGroup = uint8_t(v[11]); p.stages = uint8_t(v[12]); p.splitkFactor = uint16_t(v[13]);
         p.swizzleOffset = uint8_t(v[14]); p.swizzleDirection = uint8_t(v[15]);
         p.dtype = uint8_t(v[16]); p.outDtype = uint8_t(v[17]); p.layoutTagB = uint8_t(v[18]);
+        // only the multicast cluster is a choice; every other value is derived by finalize_plan
+        p.clusterShape = v.size() == kAllColumns && v[19] == 4 ? 4 : 0;
     } else {
         // a reference-format row: Ascend tile sizes are not meaningful here; keep the key, re-select the rest
         p.dtype = ACL_BF16; p.outDtype = ACL_BF16; p.layoutTagB = 1;

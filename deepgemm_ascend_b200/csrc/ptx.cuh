@@ -201,6 +201,27 @@ __device__ __forceinline__ void tma_load_2d_pair(const void* desc, uint64_t* bar
         :: "r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(desc)), "r"(bar_addr),
            "r"(c0), "r"(c1), "l"(hint) : "memory");
 }
+// The same load delivered to the same shared-memory offset of every CTA in `cta_mask` (cluster ranks); each
+// destination's bytes complete on the barrier at this offset in the leader (even rank) of ITS pair.  Two pairs of
+// a 4-CTA cluster fetch one half each of an operand box both need and hand the other half to each other.
+__device__ __forceinline__ void tma_load_2d_pair_multicast(const void* desc, uint64_t* bar, void* smem, int32_t c0,
+                                                           int32_t c1, uint16_t cta_mask, uint64_t hint = kEvictNormal) {
+    uint32_t bar_addr = smem_u32(bar) & 0xFEFFFFFFu;
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        ".L2::cache_hint [%0], [%1, {%4, %5}], [%2], %3, %6;"
+        :: "r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(desc)), "r"(bar_addr), "h"(cta_mask),
+           "r"(c0), "r"(c1), "l"(hint) : "memory");
+}
+// cta_group::1 flavour: every destination's bytes complete on the barrier at this offset in that destination.
+__device__ __forceinline__ void tma_load_2d_multicast(const void* desc, uint64_t* bar, void* smem, int32_t c0,
+                                                      int32_t c1, uint16_t cta_mask, uint64_t hint = kEvictNormal) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        ".L2::cache_hint [%0], [%1, {%4, %5}], [%2], %3, %6;"
+        :: "r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(desc)), "r"(smem_u32(bar)), "h"(cta_mask),
+           "r"(c0), "r"(c1), "l"(hint) : "memory");
+}
 __device__ __forceinline__ void tma_load_3d(const void* desc, uint64_t* bar, void* smem,
                                             int32_t c0, int32_t c1, int32_t c2, uint64_t hint = kEvictNormal) {
     asm volatile(
@@ -338,6 +359,17 @@ __device__ __forceinline__ void mma_commit(uint64_t* bar) {
         asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                      :: "r"(smem_u32(bar)), "h"(mask) : "memory");
     }
+}
+// ... one arrival on the barrier at this offset in every CTA of `cta_mask` (cluster ranks): releases a ring stage
+// that other CTAs of the cluster fill by multicast.
+template <int kCtaGroup>
+__device__ __forceinline__ void mma_commit_multicast(uint64_t* bar, uint16_t cta_mask) {
+    if constexpr (kCtaGroup == 1)
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                     :: "r"(smem_u32(bar)), "h"(cta_mask) : "memory");
+    else
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                     :: "r"(smem_u32(bar)), "h"(cta_mask) : "memory");
 }
 
 // TMEM -> registers: this warp's 32 lanes x 32 consecutive fp32 columns.

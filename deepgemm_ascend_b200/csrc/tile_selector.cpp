@@ -157,6 +157,12 @@ bool aligned16(uint64_t elems, uint32_t bytes) { return (elems * bytes) % 16 == 
 
 }  // namespace
 
+uint32_t clusters_of_four() {
+    // clusters of 4 CTAs that fit beside each other with the persistent kernel's footprint (one CTA per SM): 33 on a
+    // B200 (132 of 148 SMs: a cluster lives inside one GPC; tools/probes/cluster_occupancy.cu)
+    return platform().smCount * 33 / 148;
+}
+
 uint32_t streamk_overhead_kb(uint32_t block_n) {
     // the exposed fix-up chain (giver drains and writes, fence + flag, owner's adding pass) is ~5 us longer than a
     // plain epilogue: ~7500 clocks, in units of one K block of this tile (2 * block_n clocks)
@@ -241,6 +247,7 @@ int finalize_plan(DgaTilingPlan& p) {
         p.smemBytes = splitk_smem_bytes(m_pad, p.stages, p.splitkFactor);
         p.workspaceBytes = 0;
         p.paddingTagC = 0;   // this kernel stores C with plain st.global: any pitch will do
+        p.clusterShape = static_cast<uint8_t>(p.splitkFactor);   // the K slices of one weight tile form the cluster
     } else {
         if (p.ctaGroup != 1 && p.ctaGroup != 2) p.ctaGroup = 2;
         const uint32_t cta = p.ctaGroup;
@@ -270,6 +277,18 @@ int finalize_plan(DgaTilingPlan& p) {
         p.blockDim = std::min(tiles, hw.smCount / cta) * cta;
         p.smemBytes = common_smem_bytes(p.n1, cta, p.stages, epi_b, in_b);
         p.workspaceBytes = 0;
+        if (p.clusterShape == 4) {
+            // two CTA pairs per cluster on neighbouring N tiles, A multicast between them (gemm_sm100.cuh, kMc)
+            const bool whole = p.kernelSerial == DGA_KERNEL_COMMON || p.kernelSerial == DGA_KERNEL_SMALL ||
+                               p.kernelSerial == DGA_KERNEL_PADDING_COMMON;
+            if (cta != 2 || !whole || in_b != 2 || ceil_div(p.n, p.n1) % 2 != 0) {
+                set_error("clusterShape 4 needs a whole-tile 16-bit plan with ctaGroup 2 and an even number of N tiles");
+                return ACLNN_ERR_INNER_TILING_ERROR;
+            }
+            p.blockDim = std::min(tiles / 2, clusters_of_four()) * 4;
+        } else {
+            p.clusterShape = static_cast<uint8_t>(cta);
+        }
         if (split_reduce) {
             const uint32_t kb = ceil_div(p.k, 128 / in_b);
             if (p.splitkFactor < 2 || p.splitkFactor > 16 || p.splitkFactor > kb) {
@@ -295,7 +314,8 @@ int finalize_plan(DgaTilingPlan& p) {
             set_error("kernel variant " + std::to_string(int(p.kernelSerial)) + " is not built");
             return ACLNN_ERR_INNER_TILING_ERROR;
         } else {
-            p.kernelSerial = tiles <= hw.smCount / cta ? DGA_KERNEL_SMALL : DGA_KERNEL_COMMON;
+            p.kernelSerial = tiles <= (p.clusterShape == 4 ? 2 * clusters_of_four() : hw.smCount / cta)
+                                 ? DGA_KERNEL_SMALL : DGA_KERNEL_COMMON;
         }
         if (p.splitkFactor == 0) p.splitkFactor = 1;
     }
@@ -327,6 +347,7 @@ int select_kernel(DgaTilingPlan& p) {
     p.swizzleDirection = (p.m > p.n) ? 0 : 1;  // tiling_params.h:63-64
     p.splitkFactor = 1;
     p.stages = 0;
+    p.clusterShape = 0;   // = ctaGroup; the 4-CTA multicast cluster is taken by rule further down
     p.paddingTagA = aligned16(p.strideA, in_b) ? 0 : 1;
     p.paddingTagB = aligned16(p.strideB, in_b) ? 0 : 1;
     p.paddingTagC = aligned16(p.strideC, out_b) ? 0 : 1;

@@ -44,6 +44,9 @@ int select_kernel(DgaTilingPlan& plan);
 int finalize_plan(DgaTilingPlan& plan);
 int select_kernel_with_cache(DgaTilingPlan& plan);
 
+// Clusters of four CTAs (clusterShape 4) the device places side by side at one CTA per SM.
+uint32_t clusters_of_four();
+
 // Stream-K decomposition of `tiles` output tiles of `kb` K blocks over `clusters` clusters: the first `dp` tiles are
 // walked whole (one per cluster and wave); each of the last `sk` tiles (the ragged wave) is cut into `split` K slices
 // with aligned boundaries, dealt out round-robin.  want_split >= 2 forces the slice count (hand-set plans), else the

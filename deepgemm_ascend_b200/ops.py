@@ -283,6 +283,14 @@ class Fp8Executor:
                                           _stream_ptr(stream)), "dgaFp8BlockScaledMatmul")
         return self._keep[4]
 
+    def path(self, stream=None):
+        """Which kernel produced the last result: 'block_scaled' (power-of-two scales, applied by the tensor core)
+        or 'promotion' (arbitrary fp32 scales). Synchronises the stream."""
+        which = ctypes.c_int32(-1)
+        check(lib.dgaFp8QueryPath(ctypes.c_void_p(self._ws.data_ptr()), self._ex, _stream_ptr(stream),
+                                  ctypes.byref(which)), "dgaFp8QueryPath")
+        return "promotion" if which.value else "block_scaled"
+
     def close(self):
         if self._ex is not None:
             destroy_executor(self._ex)

@@ -231,6 +231,44 @@ def test_tile_widths_that_are_odd_multiples_of_16(dga):
     assert odd and odd[0] > max(i for i, p in enumerate(cands) if p.get("n1", 0) % 32 == 0 or "n1" not in p)
 
 
+def test_cluster_shape_rules(dga, tmp_path):
+    """clusterShape (north_star item 2, "chooses ... the cluster shape"): every plan reports the CTAs per cluster; 4 =
+    two CTA pairs sharing their A rows by TMA multicast, accepted only for whole-tile pair plans with an even number
+    of N tiles, at most 33 such clusters side by side, and it survives the CSV round trip."""
+    lib = dga._lib.lib
+    assert dga.select_kernel(4096, 7168, 2048)["clusterShape"] == 2
+    assert dga.select_kernel(128, 32768, 512)["clusterShape"] == 1
+    p64 = dga.select_kernel(64, 4096, 7168)
+    assert p64["kernelSerial"] == 3 and p64["clusterShape"] == p64["splitkFactor"]
+
+    def try_plan(m, n, k, **fields):
+        lib.dgaTilingCacheClear()
+        plan = dga._lib.TilingPlan()
+        for key, val in dga.select_kernel(m, n, k).items():
+            setattr(plan, key, val)
+        plan.stages = 0
+        plan.splitkFactor = 1
+        for key, val in fields.items():
+            setattr(plan, key, val)
+        rc = lib.dgaTilingCacheSet(ctypes.byref(plan))
+        return rc, (dga.select_kernel(m, n, k, use_cache=True) if rc == 0 else None)
+
+    rc, got = try_plan(512, 4096, 7168, kernelSerial=0, ctaGroup=2, n1=128, clusterShape=4)
+    assert rc == 0 and got["clusterShape"] == 4 and got["blockDim"] == 128          # 64 pair tiles = 32 clusters of 4
+    path = str(tmp_path / "c4.csv").encode()
+    assert lib.dgaTilingCacheSaveCsv(path) == 0
+    assert open(path.decode()).read().splitlines()[0].endswith(",layoutTagB,clusterShape")
+    rc, got = try_plan(4096, 7168, 2048, kernelSerial=0, ctaGroup=2, n1=256, clusterShape=4)
+    assert rc == 0 and got["blockDim"] == 33 * 4 and got["kernelSerial"] == 0      # 224 column groups on 33 clusters
+    assert try_plan(4096, 7168, 2048, kernelSerial=0, ctaGroup=1, n1=256, clusterShape=4)[0] != 0   # needs CTA pairs
+    assert try_plan(512, 384, 7168, kernelSerial=0, ctaGroup=2, n1=128, clusterShape=4)[0] != 0     # 3 N tiles: odd
+    assert try_plan(2048, 4096, 7168, kernelSerial=4, ctaGroup=2, n1=256, splitkFactor=2, clusterShape=4)[0] != 0
+    lib.dgaTilingCacheClear()
+    assert lib.dgaTilingCacheLoadCsv(path) == 0
+    assert dga.select_kernel(512, 4096, 7168, use_cache=True)["clusterShape"] == 4
+    lib.dgaTilingCacheClear()
+
+
 def test_cache_first_writer_wins_and_csv_round_trip(dga, tmp_path):
     lib = dga._lib.lib
     lib.dgaTilingCacheClear()

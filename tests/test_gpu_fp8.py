@@ -97,3 +97,52 @@ def test_fp8_config4_sampled(dga):
     got = out[rows_t][:, c0:c1].float().cpu().numpy()
     assert orc.calc_diff(got, ref) < orc.CALC_DIFF_FP8
     assert orc.max_err_over_max(got, ref) < 1e-2
+
+
+def _ceil_pow2(sf):
+    """ceil_to_ue8m0 on the device: the next power of two at or above a positive fp32 scale (oracle: ceil_to_ue8m0)."""
+    bits = sf.contiguous().view(torch.int32)
+    exp = ((bits >> 23) & 0xFF) + ((bits & 0x7FFFFF) != 0).to(torch.int32)
+    return (exp.clamp(1, 254) << 23).view(torch.float32)
+
+
+def test_fp8_config4_ue8m0_sampled(dga):
+    """BASELINE config 4 at full size with UE8M0 (power-of-two) scales, i.e. per_token_cast_to_fp8(..., use_ue8m0=True):
+    the shape and the kernel (tcgen05.mma kind::mxf8f6f4.block_scale) behind the bench's `fp8` line. Sampled rows x a
+    column window against the fp64 oracle, and the library must report that the tensor-core kernel, not the software
+    promotion kernel, produced the result."""
+    m, n, k = 4096, 7168, 16384
+    gen = torch.Generator(device=DEV).manual_seed(44)
+    a = torch.randn((m, k), device=DEV, generator=gen)
+    w = torch.randn((n, k), device=DEV, generator=gen)
+    av = a.view(m, k // 128, 128)
+    a_sf = _ceil_pow2(av.abs().amax(dim=2).clamp(min=1e-4) / 448.0)
+    a8 = (av * (1.0 / a_sf).unsqueeze(2)).view(m, k).to(torch.float8_e4m3fn)
+    wv = w.view(n // 128, 128, k // 128, 128)
+    w_sf = _ceil_pow2(wv.abs().amax(dim=(1, 3)).clamp(min=1e-4) / 448.0)
+    w8 = (wv * (1.0 / w_sf)[:, None, :, None]).view(n, k).to(torch.float8_e4m3fn)
+    del a, w, av, wv
+    out = torch.empty((m, n), device=DEV, dtype=torch.bfloat16)
+    ex = dga.Fp8Executor(a8, a_sf, w8, w_sf, out)
+    before = dga.kernel_launch_count()
+    ex()
+    assert ex.path() == "block_scaled"
+    assert dga.kernel_launch_count() > before
+    rows = np.random.RandomState(3).choice(m, 16, replace=False)
+    rows_t = torch.from_numpy(rows).to(DEV)
+    # the device-side quantisation must be the oracle's: same codes and scales on the sampled rows
+    x_rows = torch.randn((m, k), device=DEV, generator=torch.Generator(device=DEV).manual_seed(44))[rows_t].cpu().numpy()
+    codes, sf = orc.per_token_cast_to_fp8(x_rows, True)
+    assert np.array_equal(sf, a_sf[rows_t].cpu().numpy())
+    assert np.array_equal(codes, a8[rows_t].view(torch.uint8).cpu().numpy())
+    for c0, c1 in ((0, 512), (3136, 3904), (6656, 7168)):   # first tile, a window straddling 224-wide tiles, last tile
+        ref = orc.fp8_block_scaled_golden(a8[rows_t].view(torch.uint8).cpu().numpy(), a_sf[rows_t].cpu().numpy(),
+                                          w8[c0:c1].view(torch.uint8).cpu().numpy(), w_sf[c0 // 128:c1 // 128].cpu().numpy())
+        got = out[rows_t][:, c0:c1].float().cpu().numpy()
+        assert orc.calc_diff(got, ref) < orc.CALC_DIFF_FP8
+        assert orc.max_err_over_max(got, ref) < 1e-2
+    # and with one scale nudged off a power of two the same executor must take the promotion kernel
+    a_sf[0, 0] *= 1.5
+    ex()
+    assert ex.path() == "promotion"
+    ex.close()

@@ -114,6 +114,14 @@ ACLNN_CASES = [
     (1000, 1000, 1000, torch.bfloat16, 1, {"kernelSerial": 5, "ctaGroup": 2, "n1": 128, "splitkFactor": 5}),
     (640, 1024, 1024, torch.float16, 0, {"kernelSerial": 5, "ctaGroup": 2, "n1": 128, "splitkFactor": 2}),
     (127, 509, 1027, torch.bfloat16, 1, {"kernelSerial": 5, "ctaGroup": 1, "n1": 128, "splitkFactor": 4}),   # + repack of A, B
+    # clusters of four CTAs: two pairs on neighbouring N tiles, A rows fetched once and multicast (clusterShape 4)
+    (512, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 0, "ctaGroup": 2, "n1": 128, "clusterShape": 4}),
+    (256, 512, 512, torch.bfloat16, 1, {"kernelSerial": 0, "ctaGroup": 2, "n1": 256, "clusterShape": 4}),
+    (2048, 4096, 2048, torch.bfloat16, 1, {"kernelSerial": 0, "ctaGroup": 2, "n1": 256, "clusterShape": 4}),  # several tiles per cluster
+    (1000, 1000, 1000, torch.bfloat16, 1, {"kernelSerial": 0, "ctaGroup": 2, "n1": 128, "clusterShape": 4}),  # ragged M, N, K
+    (300, 900, 1992, torch.float16, 1, {"kernelSerial": 0, "ctaGroup": 2, "n1": 240, "clusterShape": 4}),     # odd-16 width
+    (640, 1024, 1024, torch.float16, 0, {"kernelSerial": 0, "ctaGroup": 2, "n1": 128, "clusterShape": 4}),    # row-major mat2
+    (127, 509, 1027, torch.bfloat16, 1, {"kernelSerial": 2, "ctaGroup": 2, "n1": 64, "clusterShape": 4}),     # + repack of A, B, C
 ]
 
 
@@ -185,6 +193,11 @@ def test_selector_audit_shapes_full_size(dga, m, n, k, serial):
 def test_config5_one_shard_full_size(dga):
     """BASELINE config 5 as one rank of eight sees it: M=16384, N=57344/8, K=7168."""
     _sampled_full_size(dga, 16384, 7168, 7168, seed=5)
+
+
+def test_config5_full_width_one_gpu(dga):
+    """BASELINE config 5 whole (16384 x 57344 x 7168) on one GPU: the 1-GPU anchor of the strong-scaling curve."""
+    _sampled_full_size(dga, 16384, 57344, 7168, seed=55)
 
 
 def test_golden_vectors_framework_path(dga, golden_dir):
