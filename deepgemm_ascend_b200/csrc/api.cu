@@ -32,6 +32,10 @@ static std::atomic<int64_t> g_opt_splitk_prefetch{-1};
 static std::atomic<int64_t> g_opt_pdl{-1};
 static std::atomic<int64_t> g_opt_splitk_batch{-1};
 static std::atomic<int64_t> g_opt_raster{-1};   // raster_group override (sweeps)
+static std::atomic<int64_t> g_opt_sk_coop{1};       // stream-K launches are cooperative (co-residency guaranteed)
+static std::atomic<int64_t> g_opt_raster_dir{-1};   // raster_along_m override (sweeps)
+static std::atomic<int64_t> g_opt_hint_a{-1}, g_opt_hint_b{-1};   // L2 eviction hints of the fp8 operand loads: 0 normal, 1 first, 2 last
+static uint64_t hint_code(int64_t v) { return v == 1 ? ptx::kEvictFirst : v == 2 ? ptx::kEvictLast : 0ull; }
 static std::atomic<int64_t> g_opt_jit{-1};      // shape-specialised kernels compiled at run time (default: $DGA_JIT)
 static bool jit_enabled() {
     static const bool env = [] { const char* e = std::getenv("DGA_JIT"); return e != nullptr && std::atoi(e) != 0; }();
@@ -161,39 +165,60 @@ struct DenseLaunch {
 // DGA_DEBUG_FLAGS & 16: every CTA of the persistent kernel writes six timestamps (see GemmParams::trace); the last
 // launch's records are read back with dgaDebugReadTrace.  Developer aid for launch-ramp / tail / clock questions.
 constexpr uint32_t kTraceWords = 6 * 1024;
+static int current_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return dev;
+}
+// one buffer per device (a process may drive several GPUs)
 static unsigned long long* trace_buffer() {
-    static unsigned long long* buf = [] {
-        void* p = nullptr;
-        if (cudaMalloc(&p, kTraceWords * 8) != cudaSuccess) return static_cast<unsigned long long*>(nullptr);
-        cudaMemset(p, 0, kTraceWords * 8);
-        return static_cast<unsigned long long*>(p);
-    }();
-    return buf;
+    static std::mutex mu;
+    static std::map<int, unsigned long long*> bufs;
+    std::lock_guard<std::mutex> lock(mu);
+    const int dev = current_device();
+    auto it = bufs.find(dev);
+    if (it != bufs.end()) return it->second;
+    void* p = nullptr;
+    if (cudaMalloc(&p, kTraceWords * 8) != cudaSuccess) return nullptr;
+    cudaMemset(p, 0, kTraceWords * 8);
+    return bufs[dev] = static_cast<unsigned long long*>(p);
 }
 
 // Launch attributes shared by every tensor-core kernel: the cluster shape and programmatic dependent launch (the
 // kernels call griddepcontrol.wait before their first global access, so the prologue of launch i+1 overlaps the
 // tail of launch i on the same stream).  DGA_PDL=0 turns the second one off (A/B measurements).
-static void fill_launch_attrs(cudaLaunchConfig_t& cfg, cudaLaunchAttribute (&attr)[2], uint32_t cluster) {
+// `co_resident`: the grid's CTAs wait on one another (stream-K owners spin on their givers' flags), so every CTA must
+// be on the machine at once whatever else runs there (another stream's GEMM, an NCCL kernel, a second stream-K
+// launch whose owners wait for THEIR givers): a cooperative launch starts only when the whole grid fits.  Such a
+// launch is not also a programmatic dependent one (it could not start under its predecessor anyway).
+static void fill_launch_attrs(cudaLaunchConfig_t& cfg, cudaLaunchAttribute (&attr)[2], uint32_t cluster,
+                              bool co_resident = false) {
     static const bool pdl = [] { const char* e = std::getenv("DGA_PDL"); return e == nullptr || std::atoi(e) != 0; }();
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = cluster;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    if (co_resident && g_opt_sk_coop.load(std::memory_order_relaxed) != 0) {
+        attr[1].id = cudaLaunchAttributeCooperative;
+        attr[1].val.cooperative = 1;
+        cfg.numAttrs = 2;
+        return;
+    }
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
     const int64_t opt = g_opt_pdl.load(std::memory_order_relaxed);
     cfg.numAttrs = (opt >= 0 ? opt != 0 : pdl) ? 2 : 1;
 }
 
-// cudaFuncSetAttribute costs microseconds of host time; remember the largest opt-in per kernel instance.
+// cudaFuncSetAttribute costs microseconds of host time; remember the largest opt-in per kernel instance and
+// device (the attribute applies to the current device only).
 template <typename K>
 static int set_smem_attr(K kernel, uint32_t bytes) {
     static std::mutex mu;
-    static std::map<const void*, uint32_t> granted;
+    static std::map<std::pair<const void*, int>, uint32_t> granted;
     std::lock_guard<std::mutex> lock(mu);
-    uint32_t& have = granted[reinterpret_cast<const void*>(kernel)];
+    uint32_t& have = granted[std::make_pair(reinterpret_cast<const void*>(kernel), current_device())];
     if (bytes <= have) return ACLNN_SUCCESS;
     DGA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
     have = bytes;
@@ -232,9 +257,9 @@ static int launch_jit(const DenseLaunch& L, const GemmParams& gp, cudaStream_t s
     }
     {
         static std::mutex mu;
-        static std::map<cudaKernel_t, uint32_t> granted;
+        static std::map<std::pair<cudaKernel_t, int>, uint32_t> granted;
         std::lock_guard<std::mutex> lock(mu);
-        uint32_t& have = granted[kernel];
+        uint32_t& have = granted[std::make_pair(kernel, current_device())];
         if (L.plan.smemBytes > have) {
             DGA_CUDA(cudaFuncSetAttribute(reinterpret_cast<const void*>(kernel),
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, int(L.plan.smemBytes)));
@@ -279,7 +304,7 @@ static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaSt
     cfg.dynamicSmemBytes = L.plan.smemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
-    fill_launch_attrs(cfg, attr, kMc ? 4 : kCta);
+    fill_launch_attrs(cfg, attr, kMc ? 4 : kCta, /*co_resident=*/kSk);
     DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, L.tm_a, L.tm_b, L.peers, gp));  // no scale maps here
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
@@ -555,6 +580,10 @@ static int launch_variant(DenseLaunch& L, cudaStream_t stream, void* workspace) 
                 set_error("the stream-K / split-K variants need their workspace");
                 return ACLNN_ERR_PARAM_INVALID;
             }
+            if ((reinterpret_cast<uintptr_t>(workspace) & 15) != 0) {   // 16-byte vector stores / TMA slabs
+                set_error("the stream-K / split-K workspace must be 16-byte aligned");
+                return ACLNN_ERR_PARAM_INVALID;
+            }
             return launch_common(L, stream, workspace);
         case DGA_KERNEL_SPLITK: return launch_splitk(L, stream);
     }
@@ -664,11 +693,12 @@ static void plan_fp8(Fp8Launch& L) {
         }
     }
     const uint32_t per_stage = 128 * 128 + (L.bn / L.cta) * 128;
-    const uint32_t fixed = 4 * 128 * 32 * 2 + 1024 + 256;
+    const uint32_t kb_count = ceil_div(L.k, 128);
+    const uint32_t fixed = 4 * 128 * 32 * 2 + 1024 + 256 + 2 * 3 * round_up(kb_count, 4) * 4;   // + weight scales of 2 tiles
     L.stages = std::min<uint32_t>(10, (hw.smemBytes - fixed) / per_stage);
     const uint32_t tiles = ceil_div(L.m, 128 * L.cta) * ceil_div(L.n, L.bn);
     L.grid = std::min(tiles, hw.smCount / L.cta) * L.cta;
-    L.smem = make_fp8_smem(L.bn, L.cta, L.stages).total + 1024;
+    L.smem = make_fp8_smem(L.bn, L.cta, L.stages, kb_count).total + 1024;
 
     // block-scaled plan
     if (L.m <= 128) {
@@ -835,6 +865,9 @@ static int launch_fp8(Fp8Launch& L, void* workspace, cudaStream_t stream) {
         gp.num_n_blocks = n_tiles;
         gp.raster_group = g_opt_raster.load(std::memory_order_relaxed) > 0 ? uint32_t(g_opt_raster.load()) : 8u;
         gp.raster_along_m = L.m > L.n ? 0 : 1;
+        if (g_opt_raster_dir.load(std::memory_order_relaxed) >= 0) gp.raster_along_m = uint32_t(g_opt_raster_dir.load());
+        gp.hint_a = hint_code(g_opt_hint_a.load(std::memory_order_relaxed));
+        gp.hint_b = hint_code(g_opt_hint_b.load(std::memory_order_relaxed));
         // block-scaled instruction descriptor: e4m3 x e4m3, UE8M0 scales (bit 23), N >> 3 at [17,23), M >> 4 at [24,29)
         gp.idesc = (1u << 23) | ((L.mx_bn >> 3) << 17) | (((128u * L.mx_cta) >> 4) << 24);
         gp.b_stage_bytes = (L.mx_bn / L.mx_cta) * 128;
@@ -1574,6 +1607,10 @@ aclnnStatus dgaSetOption(const char* name, int64_t value) {
     else if (std::strcmp(name, "pdl") == 0) g_opt_pdl.store(value);
     else if (std::strcmp(name, "splitk_issue_batch") == 0) g_opt_splitk_batch.store(value);
     else if (std::strcmp(name, "raster_group") == 0) g_opt_raster.store(value);
+    else if (std::strcmp(name, "raster_along_m") == 0) g_opt_raster_dir.store(value);
+    else if (std::strcmp(name, "streamk_cooperative") == 0) g_opt_sk_coop.store(value < 0 ? 1 : value);
+    else if (std::strcmp(name, "hint_a") == 0) g_opt_hint_a.store(value);
+    else if (std::strcmp(name, "hint_b") == 0) g_opt_hint_b.store(value);
     else if (std::strcmp(name, "jit") == 0) g_opt_jit.store(value);
     else {
         set_error(std::string("unknown option ") + name);

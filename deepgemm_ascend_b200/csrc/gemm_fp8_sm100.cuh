@@ -38,19 +38,41 @@ struct Fp8Params {
 };
 
 struct Fp8Smem {
-    uint32_t d_stage_bytes, a_stage_bytes, b_stage_bytes, off_d, off_a, off_b, off_bar, total;
+    uint32_t d_stage_bytes, a_stage_bytes, b_stage_bytes, sfb_pitch, off_d, off_a, off_b, off_sfb, off_bar, total;
 };
-__host__ __device__ inline Fp8Smem make_fp8_smem(uint32_t block_n, uint32_t cta, uint32_t stages) {
+// k_blocks: the weight scales of a tile (its columns touch at most three 128-wide scale rows) sit in shared memory,
+// two tiles deep: [2][3][sfb_pitch] floats
+__host__ __device__ inline Fp8Smem make_fp8_smem(uint32_t block_n, uint32_t cta, uint32_t stages, uint32_t k_blocks) {
     Fp8Smem l;
     l.d_stage_bytes = kBlockM * kEpiCols * 2;   // bf16 staging chunk, 2 per warp group
     l.a_stage_bytes = kBlockM * 128;
     l.b_stage_bytes = (block_n / cta) * 128;
+    l.sfb_pitch = (k_blocks + 3u) & ~3u;
     l.off_d = 0;
     l.off_a = 4 * l.d_stage_bytes;
     l.off_b = l.off_a + stages * l.a_stage_bytes;
-    l.off_bar = l.off_b + stages * l.b_stage_bytes;
+    l.off_sfb = l.off_b + stages * l.b_stage_bytes;
+    l.off_bar = l.off_sfb + 2 * 3 * l.sfb_pitch * 4;
     l.total = l.off_bar + (2 * stages + 4) * 8 + 16;
     return l;
+}
+
+// Scales of four consecutive K blocks of one scale row: one 16-byte load when the row allows it.  Issued a whole
+// group (4 K blocks of MMAs, ~2000 clocks) before first use, so the L2 round trip never sits in the promotion
+// chain.  (Round 1 fetched one float per K block two blocks ahead and rotated it through registers: the rotation
+// waited on the youngest load, every K block paid an L2 latency, and the kernel ran at 2500 clocks per K block
+// against 450 of MMAs: profiles/r02_fp8_promo_ncu_*.)
+__device__ __forceinline__ float4 load_scales4(const float* row, uint32_t kb, uint32_t k_blocks, bool vec) {
+    if (vec && kb + 4 <= k_blocks) return __ldg(reinterpret_cast<const float4*>(row + kb));
+    float4 v;
+    v.x = __ldg(row + min(kb, k_blocks - 1));
+    v.y = __ldg(row + min(kb + 1, k_blocks - 1));
+    v.z = __ldg(row + min(kb + 2, k_blocks - 1));
+    v.w = __ldg(row + min(kb + 3, k_blocks - 1));
+    return v;
+}
+__device__ __forceinline__ float pick4(const float4& v, uint32_t i) {
+    return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w;
 }
 
 __device__ __forceinline__ void stage_row_bf16(uint32_t stage_base, uint32_t row, const float (&v)[32]) {
@@ -95,7 +117,7 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
     const uint32_t stages = p.num_stages;
     const uint32_t k_blocks = p.k_blocks;
 
-    const Fp8Smem L = make_fp8_smem(kBN, kCta, stages);
+    const Fp8Smem L = make_fp8_smem(kBN, kCta, stages, k_blocks);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.off_bar);
     uint64_t* empty_bar = full_bar + stages;
     uint64_t* part_full_bar = empty_bar + stages;    // [2] partial product of one K block is in TMEM
@@ -201,10 +223,47 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
         const uint32_t bar_id = 1 + group;
         const uint32_t sbase0 = smem_base + L.off_d + group * 2 * L.d_stage_bytes;
         uint8_t* sptr0 = smem + L.off_d + group * 2 * L.d_stage_bytes;
-        uint32_t pc = 0, sbuf = 0;
+        uint32_t pc = 0, sbuf = 0, tile_par = 0;
         float acc[kOwned][32];
+        // Weight scales of a tile: 3 rows x k_blocks floats, copied to shared memory by the 256 promotion threads;
+        // the copy for tile i + 1 is issued before the stores of tile i and lands behind them.
+        const uint32_t ptid = threadIdx.x - 128;
+        float* sfb_s = reinterpret_cast<float*>(smem + L.off_sfb);
+        const uint32_t sfb_total = 3 * k_blocks;
+        constexpr uint32_t kSfbPer = 6;   // elements per thread and pass
+        auto sfb_src = [&](uint32_t tile, uint32_t idx) {
+            uint32_t mb2, nb2;
+            tile_coords(p, tile, mb2, nb2);
+            const uint32_t r = idx / k_blocks, kb = idx - r * k_blocks;
+            return p.sfb + static_cast<uint64_t>(min(((nb2 * kBN) >> 7) + r, p.sfb_rows - 1)) * p.sfb_ld + kb;
+        };
+        auto sfb_load = [&](uint32_t tile, uint32_t base, float (&v)[kSfbPer]) {
+#pragma unroll
+            for (uint32_t i = 0; i < kSfbPer; ++i) {
+                const uint32_t idx = base + ptid + i * 256;
+                if (idx < sfb_total) v[i] = __ldg(sfb_src(tile, idx));
+            }
+        };
+        auto sfb_store = [&](uint32_t par, uint32_t base, const float (&v)[kSfbPer]) {
+#pragma unroll
+            for (uint32_t i = 0; i < kSfbPer; ++i) {
+                const uint32_t idx = base + ptid + i * 256;
+                if (idx < sfb_total) {
+                    const uint32_t r = idx / k_blocks, kb = idx - r * k_blocks;
+                    sfb_s[(par * 3 + r) * L.sfb_pitch + kb] = v[i];
+                }
+            }
+        };
+        if (cluster_id < num_tiles) {
+            for (uint32_t base = 0; base < sfb_total; base += 256 * kSfbPer) {
+                float v[kSfbPer];
+                sfb_load(cluster_id, base, v);
+                sfb_store(0, base, v);
+            }
+            ptx::named_bar_sync(3, 256);
+        }
 
-        for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters) {
+        for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters, tile_par ^= 1) {
             uint32_t mb, nb;
             tile_coords(p, t, mb, nb);
             const uint32_t m0 = mb * (kBlockM * kCta) + cta_rank * kBlockM;
@@ -212,23 +271,26 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             const float* sfa_row = p.sfa + static_cast<uint64_t>(min(m0 + row, p.m - 1)) * p.sfa_ld;
             // the tile's columns touch at most three 128-wide scale blocks
             const uint32_t nblk0 = n0 >> 7;
-            const float* sfb0 = p.sfb + static_cast<uint64_t>(min(nblk0, p.sfb_rows - 1)) * p.sfb_ld;
-            const float* sfb1 = p.sfb + static_cast<uint64_t>(min(nblk0 + 1, p.sfb_rows - 1)) * p.sfb_ld;
-            const float* sfb2 = p.sfb + static_cast<uint64_t>(min(nblk0 + 2, p.sfb_rows - 1)) * p.sfb_ld;
+            const float* sfb_t = sfb_s + tile_par * 3 * L.sfb_pitch;
 #pragma unroll
             for (uint32_t ci = 0; ci < kOwned; ++ci)
 #pragma unroll
                 for (uint32_t j = 0; j < 32; ++j) acc[ci][j] = 0.f;
 
-            // scales are fetched two K blocks ahead (an L2 round trip is shorter than one block of MMAs)
-            float sa_c = __ldg(sfa_row), b0_c = __ldg(sfb0), b1_c = __ldg(sfb1), b2_c = __ldg(sfb2);
-            const uint32_t k1 = min(1u, k_blocks - 1);
-            float sa_n = __ldg(sfa_row + k1), b0_n = __ldg(sfb0 + k1), b1_n = __ldg(sfb1 + k1), b2_n = __ldg(sfb2 + k1);
+            // this row's activation scales of K blocks [4g, 4g + 4) are in registers while group g runs; group g + 1
+            // is in flight
+            const bool vec = (reinterpret_cast<uintptr_t>(p.sfa) & 15) == 0 && (p.sfa_ld & 3) == 0;
+            float4 sa4 = load_scales4(sfa_row, 0, k_blocks, vec);
+            float4 sa4n = sa4;
 
             for (uint32_t kb = 0; kb < k_blocks; ++kb, ++pc) {
-                const uint32_t k2 = min(kb + 2, k_blocks - 1);
-                const float sa_f = __ldg(sfa_row + k2), b0_f = __ldg(sfb0 + k2), b1_f = __ldg(sfb1 + k2),
-                            b2_f = __ldg(sfb2 + k2);
+                const uint32_t ki = kb & 3;
+                if (ki == 0) {
+                    if (kb != 0) sa4 = sa4n;
+                    if (kb + 4 < k_blocks) sa4n = load_scales4(sfa_row, kb + 4, k_blocks, vec);
+                }
+                const float sa_c = pick4(sa4, ki);
+                const float s0 = sa_c * sfb_t[kb], s1 = sa_c * sfb_t[L.sfb_pitch + kb], s2 = sa_c * sfb_t[2 * L.sfb_pitch + kb];
                 const uint32_t buf = pc & 1;
                 ptx::mbar_wait(&part_full_bar[buf], (pc >> 1) & 1);
                 ptx::tc_fence_after();
@@ -255,7 +317,7 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
                             }
                         }
                         const uint32_t which = ((n0 + c * 32) >> 7) - nblk0;
-                        const float s = sa_c * (which == 0 ? b0_c : which == 1 ? b1_c : b2_c);
+                        const float s = which == 0 ? s0 : which == 1 ? s1 : s2;
                         if (ci & 1) {
 #pragma unroll
                             for (uint32_t j = 0; j < 32; j += 2)
@@ -267,11 +329,12 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
                         }
                     }
                 }
-                sa_c = sa_n; b0_c = b0_n; b1_c = b1_n; b2_c = b2_n;
-                sa_n = sa_f; b0_n = b0_f; b1_n = b1_f; b2_n = b2_f;
             }
 
             // ---- tile done: registers -> bf16 -> swizzled smem -> TMA store (per warp group)
+            const uint32_t t_next = t + num_clusters;
+            float sfb_next[kSfbPer];
+            if (t_next < num_tiles) sfb_load(t_next, 0, sfb_next);
 #pragma unroll
             for (uint32_t ci = 0; ci < kOwned; ++ci) {
                 const uint32_t c = group + 2 * ci;
@@ -289,6 +352,17 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
                     }
                     sbuf ^= 1;
                 }
+            }
+            if (t_next < num_tiles) {
+                // every promotion thread is past its last read of this tile's scales' predecessor buffer: the MMA
+                // of the next tile's first K block cannot have been promoted before this point either
+                sfb_store(tile_par ^ 1, 0, sfb_next);
+                for (uint32_t base = 256 * kSfbPer; base < sfb_total; base += 256 * kSfbPer) {
+                    float v[kSfbPer];
+                    sfb_load(t_next, base, v);
+                    sfb_store(tile_par ^ 1, base, v);
+                }
+                ptx::named_bar_sync(3, 256);
             }
         }
         if (gtid == 0) ptx::tma_store_wait_all<0>();

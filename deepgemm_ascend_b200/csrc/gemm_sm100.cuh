@@ -73,6 +73,10 @@ struct GemmParams {
                              // that a workspace the caller recycled (arbitrary bytes) needs no clearing launch and
                              // cannot stall the owner; the write-back of 0 keeps CUDA-graph replays (same nonce) right
     int32_t sk_nonce;        // non-zero
+    // L2 eviction-priority hints of the operand loads (ptx::kEvict*; 0 = normal).  A panel that the tiles in flight
+    // will not touch again soon goes evict-first, the one the following waves re-read evict-last, so that the
+    // resident set of a long-K problem stays under the L2 capacity (fp8 config 4: profiles/r02_fp8_raster_sweep.log)
+    uint64_t hint_a, hint_b;
 };
 
 // N-sharded execution (BASELINE config 5): besides its own C, a rank's epilogue stores every finished chunk
@@ -350,6 +354,8 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
     ptx::grid_dep_wait();   // first global access (TMA loads, stores, stream-K workspace) comes after this
 
     const uint32_t load_n = p.block_n / kCta;  // B rows this CTA loads per stage
+    const uint64_t hint_a = p.hint_a != 0 ? p.hint_a : ptx::kEvictNormal;
+    const uint64_t hint_b = p.hint_b != 0 ? p.hint_b : ptx::kEvictNormal;
 
     if (warp == 0) {
         // ------------------------------------------------ TMA producer
@@ -407,14 +413,14 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                         if constexpr (kMc)   // 64 of this CTA's A rows, for itself and for its twin in the other pair
                             ptx::tma_load_2d_pair_multicast(&tm_a, &full_bar[stage], sa + pair * (kBlockM / 2) * kBlockKBytes,
                                                             k_idx, m_idx + static_cast<int32_t>(pair * (kBlockM / 2)),
-                                                            static_cast<uint16_t>(0x5u << cta_rank));
+                                                            static_cast<uint16_t>(0x5u << cta_rank), hint_a);
                         else
-                            ptx::tma_load_2d_pair(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
+                            ptx::tma_load_2d_pair(&tm_a, &full_bar[stage], sa, k_idx, m_idx, hint_a);
                         if constexpr (kBMn) {
                             for (uint32_t j = 0; j < load_n / 64; ++j)
-                                ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb + j * 8192, n_idx + j * 64, k_idx);
+                                ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb + j * 8192, n_idx + j * 64, k_idx, hint_b);
                         } else {
-                            ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
+                            ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb, k_idx, n_idx, hint_b);
                         }
                         if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * (L.a_stage_bytes + L.b_stage_bytes + sf_bytes));
                         else ptx::mbar_arrive_remote(&full_bar[stage], leader_rank);
@@ -630,7 +636,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                             // every giver is resident and never waits, so this ends; the deadline turns a broken
                             // invariant into a launch failure instead of a hung device
                             const volatile int32_t* flag = flag_of(first + epi_tid);
-                            const unsigned long long deadline = ptx::globaltimer() + 2000000000ull;
+                            const unsigned long long deadline = ptx::globaltimer() + 10000000000ull;   // 10 s
                             while (*flag != p.sk_nonce) {
                                 __nanosleep(64);
                                 if (ptx::globaltimer() > deadline) __trap();

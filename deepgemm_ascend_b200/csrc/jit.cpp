@@ -34,7 +34,11 @@ namespace {
 constexpr const char* kCodeName = "kernel.cu";
 constexpr const char* kBinName = "kernel.cubin";
 constexpr const char* kEntryName = "dga_jit_gemm";
-constexpr int kAbiVersion = 1;   // bump when jit_entry.cuh's contract with the host changes
+constexpr int kAbiVersion = 2;   // bump when jit_entry.cuh's contract with the host changes
+constexpr const char* kCompileFlags =
+    " -gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -lineinfo --expt-relaxed-constexpr -cubin";
+// headers the generated unit pulls in: their CONTENT is part of a cached kernel's identity
+constexpr const char* kIncluded[] = {"jit_entry.cuh", "gemm_sm100.cuh", "ptx.cuh"};
 
 std::mutex g_mu;
 std::map<std::string, cudaKernel_t> g_loaded;   // kernel_dir -> kernel (libraries stay loaded for the process)
@@ -50,15 +54,41 @@ bool exists(const std::string& path) {
     return ::stat(path.c_str(), &st) == 0;
 }
 
+// Creates the missing directories of `path` readable by the owner only.
 bool make_dirs(const std::string& path) {
     std::string cur;
     for (size_t i = 0; i <= path.size(); ++i) {
         if (i == path.size() || path[i] == '/') {
-            if (!cur.empty() && !exists(cur) && ::mkdir(cur.c_str(), 0755) != 0 && !exists(cur)) return false;
+            if (!cur.empty() && !exists(cur) && ::mkdir(cur.c_str(), 0700) != 0 && !exists(cur)) return false;
         }
         if (i < path.size()) cur.push_back(path[i]);
     }
     return true;
+}
+
+// A cache directory is trusted only if it is a real directory owned by this user that nobody else can write to:
+// binaries found there are loaded into the process (another local user must not be able to plant one).
+bool trusted_dir(const std::string& path, std::string* why) {
+    struct stat st;
+    if (::lstat(path.c_str(), &st) != 0) { *why = "cannot stat " + path; return false; }
+    if (!S_ISDIR(st.st_mode)) { *why = path + " is not a directory"; return false; }
+    if (st.st_uid != ::geteuid()) { *why = path + " belongs to another user"; return false; }
+    if ((st.st_mode & (S_IWGRP | S_IWOTH)) != 0) { *why = path + " is writable by other users"; return false; }
+    return true;
+}
+
+std::string shell_quote(const std::string& v) {
+    std::string out = "'";
+    for (char c : v) {
+        if (c == '\'') out += "'\\''"; else out.push_back(c);
+    }
+    out.push_back('\'');
+    return out;
+}
+
+uint64_t fnv1a(const std::string& data, uint64_t h = 1469598103934665603ull) {
+    for (unsigned char c : data) { h ^= c; h *= 1099511628211ull; }
+    return h;
 }
 
 std::string read_file(const std::string& path) {
@@ -97,6 +127,9 @@ const char* out_type_name(int32_t dtype) {
     }
 }
 
+std::string cache_root() { return env_or("DGA_ROOT_DIR", "/tmp/dga_b200_" + std::to_string(::getuid())); }
+std::string cache_dir() { return cache_root() + "/deep_gemm_ascend/cache"; }
+
 // Runs `command` through the shell, returns its exit status and the combined output (reference:
 // call_external_command, utils/system.hpp).
 int run_command(const std::string& command, std::string* output) {
@@ -108,13 +141,37 @@ int run_command(const std::string& command, std::string* output) {
     return status;
 }
 
+// Identity of the toolchain and of the kernel text behind every generated unit: content of the included headers,
+// the compiler's version banner and the flags.  Computed once per process.  A kernel directory written under any
+// other digest is rebuilt (its stored source no longer equals what is generated now).
+const std::string& build_digest() {
+    static const std::string digest = [] {
+        uint64_t h = fnv1a(kCompileFlags);
+        const std::string inc = include_dir();
+        for (const char* name : kIncluded) h = fnv1a(read_file(inc + "/" + name), h ^ fnv1a(name));
+        std::string banner;
+        run_command(shell_quote(compiler_path()) + " --version", &banner);
+        h = fnv1a(banner, h);
+        char buf[32];
+        std::snprintf(buf, sizeof(buf), "%016llx", static_cast<unsigned long long>(h));
+        return std::string(buf);
+    }();
+    return digest;
+}
+
 bool valid_on_disk(const std::string& dir, const std::string& code) {
-    return exists(dir + kCodeName) && exists(dir + kBinName) && read_file(dir + kCodeName) == code;
+    std::string why;
+    return exists(dir + kCodeName) && exists(dir + kBinName) && trusted_dir(cache_dir(), &why) && trusted_dir(dir, &why) &&
+           read_file(dir + kCodeName) == code;
 }
 
 bool compile(const std::string& dir, const std::string& code, std::string* err) {
     if (!make_dirs(dir)) {
         *err = "cannot create " + dir;
+        return false;
+    }
+    if (!trusted_dir(cache_dir(), err) || !trusted_dir(dir, err)) {
+        *err = "refusing the kernel cache: " + *err + " (set DGA_ROOT_DIR to a directory of your own)";
         return false;
     }
     const std::string pid = std::to_string(::getpid());
@@ -132,9 +189,8 @@ bool compile(const std::string& dir, const std::string& code, std::string* err) 
         }
     }
     const std::string tmp = dir + kBinName + ".tmp" + pid;
-    const std::string command = compiler_path() +
-        " -gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -lineinfo --expt-relaxed-constexpr -cubin -I" +
-        include_dir() + " -o " + tmp + " " + dir + kCodeName;
+    const std::string command = shell_quote(compiler_path()) + kCompileFlags + " -I" + shell_quote(include_dir()) + " -o " +
+                                shell_quote(tmp) + " " + shell_quote(dir + kCodeName);
     std::string output;
     const int status = run_command(command, &output);
     if (status != 0 || !exists(tmp)) {
@@ -166,13 +222,12 @@ std::string signature(const Request& r) {
 }
 
 std::string kernel_dir(const Request& r) {
-    const std::string root = env_or("DGA_ROOT_DIR", "/tmp/dga_b200_" + std::to_string(::getuid()));
-    return root + "/deep_gemm_ascend/cache/kernel_" + signature(r) + "/";
+    return cache_dir() + "/kernel_" + signature(r) + "/";
 }
 
 std::string generate_code(const Request& r) {
     std::ostringstream s;
-    s << "// generated by dga-b200 (jit abi " << kAbiVersion << "): " << signature(r) << "\n";
+    s << "// generated by dga-b200 (jit abi " << kAbiVersion << ", build " << build_digest() << "): " << signature(r) << "\n";
     auto def = [&s](const char* name, uint64_t v) { s << "#define DGA_JIT_" << name << " " << v << "u\n"; };
     def("M", r.m);
     def("N", r.n);

@@ -3,7 +3,14 @@
 // (op_tiling/csv.cpp:31-140).  Differences: guarded by a mutex (the reference's singleton is not
 // thread-safe), keyed on (m, n, k, dtype, outDtype, layoutTagB) (the reference keys on (m, n, k) only,
 // "todo: layout tag is key", cache.cpp:47), and the CSV keeps the reference's 11 columns
-// (csv.cpp:23-26) followed by the B200 ones.  First writer wins, like the reference (cache_test.cpp:63-85).
+// (csv.cpp:23-26) followed by the B200 ones.  First writer wins, like the reference (cache_test.cpp:63-85), with one
+// refinement: every entry remembers where it came from, and an EXPLICIT plan (dgaTilingCacheSet, a CSV row marked
+// tuned) replaces one the analytic selector inserted by itself on a miss - otherwise a tuned table loaded after
+// the first call for a shape would be silently ignored.  Among explicit writers the first still wins.
+#include <fcntl.h>
+#include <sys/file.h>
+#include <unistd.h>
+
 #include <cstdlib>
 #include <fstream>
 #include <map>
@@ -21,12 +28,19 @@ using Key = std::tuple<uint32_t, uint32_t, uint32_t, int32_t, int32_t, int32_t>;
 
 const char* kHeader =
     "m,n,k,m1,n1,k1,kernelSerial,paddingTagA,paddingTagB,paddingTagC,blockDim,"
-    "ctaGroup,stages,splitkFactor,swizzleOffset,swizzleDirection,dtype,outDtype,layoutTagB,clusterShape";
-constexpr size_t kRefColumns = 11, kR1Columns = 19, kAllColumns = 20;   // 19: tables written before clusterShape existed
+    "ctaGroup,stages,splitkFactor,swizzleOffset,swizzleDirection,dtype,outDtype,layoutTagB,clusterShape,origin";
+// 19: tables written before clusterShape existed (all of them tuned tables or hand-written: explicit);
+// origin: 0 = inserted by the analytic selector on a miss, 1 = explicit (tuned / hand-set)
+constexpr size_t kRefColumns = 11, kR1Columns = 19, kAllColumns = 21;
+enum Origin : int { kAnalytic = 0, kExplicit = 1 };
 
+struct Entry {
+    DgaTilingPlan plan;
+    int origin;
+};
 struct Cache {
     std::mutex mu;
-    std::map<Key, DgaTilingPlan> data;
+    std::map<Key, Entry> data;
     std::string file;  // append target ($CACHE_FILE_PATH), empty = disabled
     bool env_loaded = false;
 };
@@ -36,18 +50,18 @@ Cache& cache() {
 }
 Key key_of(const DgaTilingPlan& p) { return Key(p.m, p.n, p.k, p.dtype, p.outDtype, p.layoutTagB); }
 
-std::string row_of(const DgaTilingPlan& p) {
+std::string row_of(const DgaTilingPlan& p, int origin) {
     std::ostringstream os;
     os << p.m << ',' << p.n << ',' << p.k << ',' << p.m1 << ',' << p.n1 << ',' << p.k1 << ',' << int(p.kernelSerial)
        << ',' << int(p.paddingTagA) << ',' << int(p.paddingTagB) << ',' << int(p.paddingTagC) << ',' << p.blockDim
        << ',' << int(p.ctaGroup) << ',' << int(p.stages) << ',' << p.splitkFactor << ',' << int(p.swizzleOffset) << ','
        << int(p.swizzleDirection) << ',' << int(p.dtype) << ',' << int(p.outDtype) << ',' << int(p.layoutTagB) << ','
-       << int(p.clusterShape);
+       << int(p.clusterShape == 4 ? 4 : 0) << ',' << origin;
     return os.str();
 }
 
 // Parses one CSV row; accepts the reference's 11-column rows (B200 fields are then re-derived).
-bool parse_row(const std::string& line, DgaTilingPlan& p) {
+bool parse_row(const std::string& line, DgaTilingPlan& p, int& origin) {
     std::vector<long long> v;
     std::stringstream ss(line);
     std::string cell;
@@ -58,6 +72,7 @@ bool parse_row(const std::string& line, DgaTilingPlan& p) {
         v.push_back(x);
     }
     if (v.size() != kRefColumns && v.size() != kR1Columns && v.size() != kAllColumns) return false;
+    origin = v.size() == kAllColumns ? (v[20] != 0 ? kExplicit : kAnalytic) : (v.size() == kR1Columns ? kExplicit : kAnalytic);
     p = DgaTilingPlan{};
     p.m = uint32_t(v[0]); p.n = uint32_t(v[1]); p.k = uint32_t(v[2]);
     p.m1 = uint16_t(v[3]); p.n1 = uint16_t(v[4]); p.k1 = uint16_t(v[5]);
@@ -84,6 +99,32 @@ bool parse_row(const std::string& line, DgaTilingPlan& p) {
     return finalize_plan(p) == ACLNN_SUCCESS;
 }
 
+// First writer wins, except that an explicit plan replaces an analytic one.  Returns true when the map changed.
+bool insert_locked(Cache& c, const Key& key, const DgaTilingPlan& p, int origin) {
+    auto it = c.data.find(key);
+    if (it == c.data.end()) {
+        c.data.emplace(key, Entry{p, origin});
+        return true;
+    }
+    if (it->second.origin == kAnalytic && origin == kExplicit) {
+        it->second = Entry{p, origin};
+        return true;
+    }
+    return false;
+}
+
+// One row, appended under an exclusive lock with a single write: several ranks of one job share the file.
+void append_row(const std::string& path, const std::string& row) {
+    const int fd = ::open(path.c_str(), O_WRONLY | O_APPEND | O_CREAT, 0644);
+    if (fd < 0) return;
+    ::flock(fd, LOCK_EX);
+    const std::string line = row + "\n";
+    ssize_t ignored = ::write(fd, line.data(), line.size());
+    (void)ignored;
+    ::flock(fd, LOCK_UN);
+    ::close(fd);
+}
+
 int load_csv_locked(Cache& c, const std::string& path) {
     std::ifstream in(path);
     if (!in) return ACLNN_ERR_PARAM_INVALID;
@@ -97,11 +138,12 @@ int load_csv_locked(Cache& c, const std::string& path) {
             if (line.rfind("m,n,k", 0) == 0) continue;  // header
         }
         DgaTilingPlan p;
-        if (!parse_row(line, p)) {
+        int origin = kAnalytic;
+        if (!parse_row(line, p, origin)) {
             set_error("bad tiling-cache row: " + line);
             continue;
         }
-        c.data.emplace(key_of(p), p);  // first writer wins
+        insert_locked(c, key_of(p), p, origin);
     }
     return ACLNN_SUCCESS;
 }
@@ -130,21 +172,19 @@ int cache_get(DgaTilingPlan& p) {
     ensure_env_loaded(c);
     auto it = c.data.find(key_of(p));
     if (it == c.data.end()) return ACLNN_ERR_PARAM_INVALID;
-    p = it->second;
+    p = it->second.plan;
     return ACLNN_SUCCESS;
 }
 
-int cache_set(const DgaTilingPlan& p) {
+static int cache_set_as(const Key& key, const DgaTilingPlan& p, int origin) {
     Cache& c = cache();
     std::lock_guard<std::mutex> g(c.mu);
     ensure_env_loaded(c);
-    if (!c.data.emplace(key_of(p), p).second) return ACLNN_SUCCESS;  // already present: keep the first
-    if (!c.file.empty()) {
-        std::ofstream out(c.file, std::ios::app);
-        if (out) out << row_of(p) << '\n';
-    }
+    if (!insert_locked(c, key, p, origin)) return ACLNN_SUCCESS;  // already present: keep the first
+    if (!c.file.empty()) append_row(c.file, row_of(p, origin));
     return ACLNN_SUCCESS;
 }
+int cache_set(const DgaTilingPlan& p) { return cache_set_as(key_of(p), p, kExplicit); }
 
 void cache_clear() {
     Cache& c = cache();
@@ -169,7 +209,7 @@ int cache_save_csv(const char* path) {
     std::ofstream out(path);
     if (!out) return ACLNN_ERR_PARAM_INVALID;
     out << kHeader << '\n';
-    for (const auto& kv : c.data) out << row_of(kv.second) << '\n';
+    for (const auto& kv : c.data) out << row_of(kv.second.plan, kv.second.origin) << '\n';
     return ACLNN_SUCCESS;
 }
 
@@ -179,8 +219,11 @@ int select_kernel_with_cache(DgaTilingPlan& p) {
         p = hit;
         return ACLNN_SUCCESS;
     }
+    // stored under the caller's key: select_kernel canonicalises the layout of degenerate shapes (n == 1), and a
+    // later lookup arrives with the caller's layout again
+    const Key key = key_of(p);
     int rc = select_kernel(p);
-    if (rc == ACLNN_SUCCESS) cache_set(p);
+    if (rc == ACLNN_SUCCESS) cache_set_as(key, p, kAnalytic);
     return rc;
 }
 

@@ -42,6 +42,17 @@ def _stream_ptr(stream=None):
     return ctypes.c_void_p(s.cuda_stream)
 
 
+def _scratch(nbytes, device, stream):
+    """Workspace for one asynchronous launch on `stream`. torch's caching allocator hands a freed block to the next
+    allocation on the stream it was allocated on (the current one); when the launch runs on another stream the
+    block must stay reserved until that stream has passed this point, or a later allocation could overwrite
+    repack buffers, split-K slabs, stream-K partials and flags, or packed fp8 scales that the kernels still use."""
+    ws = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=device)
+    if stream is not None and stream != torch.cuda.current_stream(device):
+        ws.record_stream(stream)
+    return ws
+
+
 def _require_cuda(*tensors):
     for t in tensors:
         if not t.is_cuda:
@@ -82,7 +93,7 @@ def catlass_dynamic_matmul(self, mat2, out=None, stream=None):
     if out is None:
         out = torch.empty((self.shape[0], mat2.shape[1]), dtype=self.dtype, device=self.device)
     ws_bytes, ex = get_workspace_size(self, mat2, out)
-    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=self.device) if ws_bytes else None
+    ws = _scratch(ws_bytes, self.device, stream) if ws_bytes else None
     execute(ws, ws_bytes, ex, stream)
     return out
 
@@ -262,7 +273,7 @@ def fp8_block_scaled_matmul(a, a_scale, weight, w_scale, out=None, stream=None):
     if out is None:
         out = torch.empty((a.shape[0], weight.shape[0]), dtype=torch.bfloat16, device=a.device)
     ws_bytes, ex = fp8_get_workspace_size(a, a_scale, weight.t(), w_scale, out)
-    ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=a.device)
+    ws = _scratch(ws_bytes, a.device, stream)
     check(lib.dgaFp8BlockScaledMatmul(ctypes.c_void_p(ws.data_ptr()), ws_bytes, ex, _stream_ptr(stream)),
           "dgaFp8BlockScaledMatmul")
     return out

@@ -257,7 +257,7 @@ def test_cluster_shape_rules(dga, tmp_path):
     assert rc == 0 and got["clusterShape"] == 4 and got["blockDim"] == 128          # 64 pair tiles = 32 clusters of 4
     path = str(tmp_path / "c4.csv").encode()
     assert lib.dgaTilingCacheSaveCsv(path) == 0
-    assert open(path.decode()).read().splitlines()[0].endswith(",layoutTagB,clusterShape")
+    assert open(path.decode()).read().splitlines()[0].endswith(",layoutTagB,clusterShape,origin")
     rc, got = try_plan(4096, 7168, 2048, kernelSerial=0, ctaGroup=2, n1=256, clusterShape=4)
     assert rc == 0 and got["blockDim"] == 33 * 4 and got["kernelSerial"] == 0      # 224 column groups on 33 clusters
     assert try_plan(4096, 7168, 2048, kernelSerial=0, ctaGroup=1, n1=256, clusterShape=4)[0] != 0   # needs CTA pairs
@@ -277,24 +277,43 @@ def test_cache_first_writer_wins_and_csv_round_trip(dga, tmp_path):
     assert lib.dgaTilingCacheSize() == 1
     p2 = dga.select_kernel(2048, 4096, 7168, use_cache=True)   # select_kernel_test.cpp:94-110: a hit returns the same tile
     assert p1 == p2
-    # cache_test.cpp:63-85: a second SetTiling for the same key does not replace the first
+    # an explicit SetTiling replaces what the analytic selector inserted by itself on a miss (a tuned table loaded
+    # after the first call for a shape must not be ignored) ...
     plan = dga._lib.TilingPlan()
     for key, val in p1.items():
         setattr(plan, key, val)
-    plan.n1 = 128 if p1["n1"] != 128 else 64
+    first = 128 if p1["n1"] != 128 else 64
+    plan.n1 = first
     plan.stages = 0
     assert lib.dgaTilingCacheSet(ctypes.byref(plan)) == 0
-    assert dga.select_kernel(2048, 4096, 7168, use_cache=True)["n1"] == p1["n1"]
+    assert dga.select_kernel(2048, 4096, 7168, use_cache=True)["n1"] == first
+    # ... and cache_test.cpp:63-85: a second SetTiling for the same key does not replace the first
+    plan.n1 = 96
+    plan.stages = 0
+    assert lib.dgaTilingCacheSet(ctypes.byref(plan)) == 0
+    assert dga.select_kernel(2048, 4096, 7168, use_cache=True)["n1"] == first
+    p1 = dga.select_kernel(2048, 4096, 7168, use_cache=True)
     dga.select_kernel(64, 4096, 7168, use_cache=True)
+    # degenerate shapes are stored under the caller's layout (the selector canonicalises n == 1 to the K-major reading)
+    size = lib.dgaTilingCacheSize()
+    dga.select_kernel(256, 1, 512, layout_b=0, use_cache=True)
+    dga.select_kernel(256, 1, 512, layout_b=0, use_cache=True)
+    assert lib.dgaTilingCacheSize() == size + 1
+    got = dga._lib.TilingPlan()
+    assert lib.dgaTilingCacheGet(256, 1, 512, dga._lib.ACL_BF16, dga._lib.ACL_BF16, 0, ctypes.byref(got)) == 0
     path = str(tmp_path / "tiling.csv").encode()
     assert lib.dgaTilingCacheSaveCsv(path) == 0
     text = open(path.decode()).read().splitlines()
     # the reference's 11 columns come first (csv.cpp:23-26, csv_test.cpp:31-37)
     assert text[0].startswith("m,n,k,m1,n1,k1,kernelSerial,paddingTagA,paddingTagB,paddingTagC,blockDim")
-    assert len(text) == 3
+    assert text[0].endswith(",clusterShape,origin")
+    assert len(text) == 4
+    assert sorted(row.rsplit(",", 1)[1] for row in text[1:]) == ["0", "0", "1"]   # two analytic rows, one explicit
     lib.dgaTilingCacheClear()
+    # a table loaded AFTER the analytic selector has answered for a shape still takes effect
+    assert dga.select_kernel(2048, 4096, 7168, use_cache=True)["n1"] != first
     assert lib.dgaTilingCacheLoadCsv(path) == 0
-    assert lib.dgaTilingCacheSize() == 2
+    assert lib.dgaTilingCacheSize() == 3
     back = dga.select_kernel(2048, 4096, 7168, use_cache=True)
     back.pop("estTimeUs"); want = dict(p1); want.pop("estTimeUs")   # the estimate is not persisted
     assert back == want

@@ -294,6 +294,34 @@ def test_stream_k_tolerates_a_dirty_workspace_and_graph_replay(dga):
     exe.close()
 
 
+def test_side_stream_launch_keeps_its_workspace(dga):
+    """The one-shot operator call allocates its workspace itself. Launched on a stream that is not torch's current
+    one, the block must stay reserved until that stream is done with it: here the current stream keeps allocating
+    and overwriting same-sized blocks while a queue of split-K + reduce launches (fp32 slabs in the workspace) is
+    still pending on the side stream."""
+    m, n, k = 256, 2048, 7168
+    plan = dga.select_kernel(m, n, k)
+    assert plan["kernelSerial"] == 5 and plan["workspaceBytes"] > 0
+    a, b = _inputs(m, n, k, torch.bfloat16, seed=31)
+    ta, w = _to_dev(a, torch.bfloat16), _to_dev(b.T, torch.bfloat16)
+    ref = orc.golden_fp64(a, b)
+    side = torch.cuda.Stream()
+    outs = [torch.zeros((m, n), dtype=torch.bfloat16, device=DEV) for _ in range(12)]
+    blocker = torch.randn((8192, 8192), device=DEV)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        for _ in range(6):
+            blocker = blocker @ blocker * 1e-4          # keeps the side stream busy: the GEMMs below queue up
+    for out in outs:
+        dga.catlass_dynamic_matmul(ta, w.t(), out=out, stream=side)
+        junk = torch.empty(plan["workspaceBytes"], dtype=torch.uint8, device=DEV)   # current stream: same size class
+        junk.fill_(0x7F)
+        del junk
+    torch.cuda.synchronize()
+    for out in outs:
+        assert orc.max_rel_err(out.float().cpu().numpy(), ref) <= 2.0 ** -7
+
+
 def test_executor_repeatable_and_graph_capturable(dga):
     a, b = _inputs(256, 512, 256, torch.bfloat16, seed=9)
     ta, w = _to_dev(a, torch.bfloat16), _to_dev(b.T, torch.bfloat16)
