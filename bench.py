@@ -1,15 +1,22 @@
 #!/usr/bin/env python3
 """bench.py -- headline benchmark of the B200 dynamic-shape matmul (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME] [--sustain-seconds S]
 
 A step is one pass of the hot path over one batch: one GEMM launch through the reference-facing two-phase C ABI
 (aclnnCatlassDynamicMatmulGetWorkspaceSize once, aclnnCatlassDynamicMatmul per step).
 Workloads (BASELINE.json configs):
-  config2 (default)  bf16 M=4096 N=7168 K=2048, weight stored [N,K]; with --gpus g the weight is N-sharded:
+  auto (default)     one GPU: config2, the configuration BASELINE.json's metric is quoted on.  --gpus g > 1: config5,
+                     the N-sharded shape north_star item 4 names, STRONG-scaled over the g ranks.  Either way the line
+                     carries a "config5" block with the 1-GPU anchor (the whole 16384 x 57344 x 7168 GEMM on one GPU,
+                     measured in the same process), so the strong-scaling curve has its N = 1 point at every N.
+  config2            bf16 M=4096 N=7168 K=2048, weight stored [N,K]; with --gpus g the weight is N-sharded:
                      every rank owns a 7168-column slice of a 7168*g wide weight (weak scaling, no data-path
                      collective; the optional all-gather of C is timed separately and reported under "allgather")
-  config5            bf16 M=16384 N=57344 K=7168, N-sharded over --gpus ranks (strong scaling) + all-gather of C
+  config5            bf16 M=16384 N=57344 K=7168; one GPU: the whole GEMM; g ranks: weight N-sharded, a step = GEMM
+                     with the all-gather of C fused into its epilogue (dgaNShardMatmul) + cross-rank barrier
+  repack             bf16 1279 x 5003 x 7681, the reference's first odd benchmark shape (benchmark.py:41-43): no operand
+                     has a 16-byte aligned pitch, all three go through the stride repack (PaddingCommon)
   m<M>               bf16 M in {1,16,...} at N=4096 K=7168 (dynamic-M sweep point; CUDA-graph of 20 launches per step)
   fp8                e4m3 block-scaled M=4096 N=7168 K=16384, UE8M0 (power-of-two) scales -> tensor-core block scaling
   fp8_fp32scales     same shape, arbitrary fp32 scales -> software promotion kernel
@@ -25,11 +32,11 @@ import sys
 import threading
 import time
 
-if "reference" in sys.argv[1:]:
-    # torch.distributed.run exports OMP_NUM_THREADS=1 to every rank it starts; the reference arm is the CPU golden
-    # "with all the host threads it can use", so the BLAS pool must be sized before numpy loads it
-    for _var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
-        os.environ.pop(_var, None)
+# torch.distributed.run exports OMP_NUM_THREADS=1 to every rank it starts; the CPU golden (the reference arm, and the
+# cpu_baseline leg of ours) runs "with all the host threads it can use", so the BLAS pool must be sized before numpy
+# loads it
+for _var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+    os.environ.pop(_var, None)
 
 import numpy as np
 
@@ -52,7 +59,17 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
+def resolve_workload(name, world):
+    """"auto": BASELINE.json's headline configuration on one GPU, its N-sharded configuration on several."""
+    if name == "auto":
+        return "config2" if world == 1 else "config5"
+    return name
+
+
 def workload_shape(name, world):
+    name = resolve_workload(name, world)
+    if name == "repack":
+        return dict(m=1279, n=5003, k=7681, dtype="bf16", n_total=5003 * world, scaling="weak")
     if name == "config2":
         return dict(m=4096, n=7168, k=2048, dtype="bf16", n_total=7168 * world, scaling="weak")
     if name == "config5":
@@ -126,17 +143,23 @@ class ClockSampler(threading.Thread):
 
 
 # ------------------------------------------------------------------------------------------- CPU baseline
+_GOLDEN_INPUTS = {}   # inputs of the last sample (generated once per run, not per step)
+
+
 def cpu_golden_run(shape, budget_s, max_reps):
     """The reference's CPU golden for this path: np.matmul of the fp16 inputs widened to fp32
     (deep_gemm_ascend/scripts/gen_golden.py:14-15), restated in oracle.matmul_oracle.golden_fp32, on all host cores.
-    Bounded sample: M is cut so that one repetition is ~<= 60 GFLOP, repeated until the budget is used."""
+    The whole problem when one repetition is <= 150 GFLOP (config 2: all 4096 rows, ~0.13 s); beyond that a bounded
+    sample: M is cut so that one repetition is ~60 GFLOP over the full N and K. Repeated until the budget is used."""
     from oracle import matmul_oracle as orc
-    m, n, k = shape["m"], shape["n"], shape["k"]
-    rows = max(1, min(m, int(60e9 / (2.0 * n * k))))
-    rng = np.random.RandomState(0)
-    x1 = rng.uniform(1, 10, [rows, k]).astype(np.float16)
-    x2 = rng.uniform(1, 10, [k, n]).astype(np.float16)
-    orc.golden_fp32(x1[: max(1, rows // 8)], x2)  # warm the BLAS threads
+    m, n, k = shape["m"], shape["n_total"] if shape["scaling"] == "strong" else shape["n"], shape["k"]
+    rows = m if 2.0 * m * n * k <= 150e9 else max(1, min(m, int(60e9 / (2.0 * n * k))))
+    if _GOLDEN_INPUTS.get("key") != (rows, n, k):
+        rng = np.random.RandomState(0)
+        _GOLDEN_INPUTS.update(key=(rows, n, k), x1=rng.uniform(1, 10, [rows, k]).astype(np.float16),
+                              x2=rng.random_sample([k, n]).astype(np.float16) * np.float16(9) + np.float16(1))
+        orc.golden_fp32(_GOLDEN_INPUTS["x1"][: max(1, rows // 8)], _GOLDEN_INPUTS["x2"])  # warm the BLAS threads
+    x1, x2 = _GOLDEN_INPUTS["x1"], _GOLDEN_INPUTS["x2"]
     t0 = time.perf_counter()
     reps = 0
     while reps < max_reps and (time.perf_counter() - t0 < budget_s or reps == 0):
@@ -160,7 +183,6 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     shape = workload_shape(args.workload, world)
-    flops, _ = algorithmic(shape)
     base, _ = cpu_golden_run(shape, budget_s=2.0, max_reps=2)  # warm-up, also sizes the sample
     per_step = []
     rows = None
@@ -174,7 +196,7 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "TFLOP/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": shape["scaling"], "vs_baseline": None, "dtype": "f32 (CPU golden of fp16/bf16 inputs)",
-            "data": "synthetic", "config": {"workload": describe(args.workload, shape, world)},
+            "data": "synthetic", "config": config_of(args.workload, shape, world),
             "cpu_baseline": {"value": value, "unit": "TFLOP/s", "cores": base["cores"], "kind": "port",
                              "sample": rows},
             "e2e": {"value": value, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -184,7 +206,16 @@ def run_reference(args, rank, world):
 
 def describe(name, shape, world):
     return "%s: %s M=%d N=%d K=%d per GPU (N_total=%d over %d GPU%s), weight stored [N,K]" % (
-        name, shape["dtype"], shape["m"], shape["n"], shape["k"], shape["n_total"], world, "" if world == 1 else "s")
+        resolve_workload(name, world), shape["dtype"], shape["m"], shape["n"], shape["k"], shape["n_total"], world,
+        "" if world == 1 else "s")
+
+
+def config_of(name, shape, world):
+    """The `config` object: what is measured, the same in both arms (arm-specific detail goes under "run")."""
+    return {"workload": describe(name, shape, world), "m": shape["m"], "n_per_gpu": shape["n"], "k": shape["k"],
+            "n_total": shape["n_total"], "scaling": shape["scaling"],
+            "l2_policy": "GPU arm: operands of consecutive steps rotate over buffer sets whose total exceeds 2x the "
+                         "126 MB L2, or one set exceeds it (config5); CPU arm: operands exceed the host's last-level cache"}
 
 
 def main():
@@ -193,8 +224,11 @@ def main():
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="config2")
+    ap.add_argument("--workload", default="auto")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sustain-seconds", type=float, default=2.0,
+                    help="length of the back-to-back run behind the `sustained` block of the default line (0 = skip)")
+    ap.add_argument("--no-config5", action="store_true", help="skip the 1-GPU config-5 anchor of the default line")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))

@@ -34,7 +34,7 @@ static std::atomic<int64_t> g_opt_splitk_batch{-1};
 static std::atomic<int64_t> g_opt_raster{-1};   // raster_group override (sweeps)
 static std::atomic<int64_t> g_opt_sk_coop{1};       // stream-K launches are cooperative (co-residency guaranteed)
 static std::atomic<int64_t> g_opt_raster_dir{-1};   // raster_along_m override (sweeps)
-static std::atomic<int64_t> g_opt_hint_a{-1}, g_opt_hint_b{-1};   // L2 eviction hints of the fp8 operand loads: 0 normal, 1 first, 2 last
+static std::atomic<int64_t> g_opt_hint_a{-1}, g_opt_hint_b{-1};   // L2 eviction hints of the operand loads: 0 normal, 1 first, 2 last (-1: the walk rule's)
 static uint64_t hint_code(int64_t v) { return v == 1 ? ptx::kEvictFirst : v == 2 ? ptx::kEvictLast : 0ull; }
 static std::atomic<int64_t> g_opt_jit{-1};      // shape-specialised kernels compiled at run time (default: $DGA_JIT)
 static bool jit_enabled() {
@@ -409,6 +409,9 @@ static void common_params(const DgaTilingPlan& p, GemmParams& gp) {
     gp.raster_group = p.swizzleOffset;
     if (g_opt_raster.load(std::memory_order_relaxed) > 0) gp.raster_group = uint32_t(g_opt_raster.load());
     gp.raster_along_m = p.swizzleDirection;
+    if (g_opt_raster_dir.load(std::memory_order_relaxed) >= 0) gp.raster_along_m = uint32_t(g_opt_raster_dir.load());
+    if (g_opt_hint_a.load(std::memory_order_relaxed) >= 0) gp.hint_a = hint_code(g_opt_hint_a.load());
+    if (g_opt_hint_b.load(std::memory_order_relaxed) >= 0) gp.hint_b = hint_code(g_opt_hint_b.load());
     gp.idesc = make_idesc(128 * cta, p.n1, p.dtype == ACL_BF16 ? 1u : 0u, 0, p.layoutTagB == 1 ? 0u : 1u);
     gp.b_stage_bytes = (p.n1 / cta) * 128;
     gp.k_block_elems = 64;
@@ -820,7 +823,8 @@ static int launch_fp8(Fp8Launch& L, void* workspace, cudaStream_t stream) {
     if (!L.encoded) {
         int rc = make_tmap_2d(&L.tm_a, L.a, ACL_FLOAT8_E4M3FN, L.k, L.m, L.lda, 128, 128, CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc != ACLNN_SUCCESS) return rc;
-        rc = make_tmap_2d(&L.tm_b, L.b, ACL_FLOAT8_E4M3FN, L.k, L.n, L.ldb, 128, L.bn / L.cta, CU_TENSOR_MAP_SWIZZLE_128B);
+        // promotion kernel: two boxes of bn / (2 cta) weight rows per CTA and stage, one per column half
+        rc = make_tmap_2d(&L.tm_b, L.b, ACL_FLOAT8_E4M3FN, L.k, L.n, L.ldb, 128, L.bn / (2 * L.cta), CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc != ACLNN_SUCCESS) return rc;
         rc = make_tmap_2d(&L.tm_b_mx, L.b, ACL_FLOAT8_E4M3FN, L.k, L.n, L.ldb, 128, L.mx_bn / L.mx_cta,
                           CU_TENSOR_MAP_SWIZZLE_128B);
@@ -863,11 +867,13 @@ static int launch_fp8(Fp8Launch& L, void* workspace, cudaStream_t stream) {
         gp.k_blocks = kb_total;
         gp.num_m_blocks = ceil_div(L.m, 128 * L.mx_cta);
         gp.num_n_blocks = n_tiles;
-        gp.raster_group = g_opt_raster.load(std::memory_order_relaxed) > 0 ? uint32_t(g_opt_raster.load()) : 8u;
-        gp.raster_along_m = L.m > L.n ? 0 : 1;
+        const WalkOrder walk = choose_walk(gp.num_m_blocks, gp.num_n_blocks, uint64_t(128) * L.mx_cta * L.k,
+                                           uint64_t(L.mx_bn) * L.k, L.m > L.n);
+        gp.raster_group = g_opt_raster.load(std::memory_order_relaxed) > 0 ? uint32_t(g_opt_raster.load()) : walk.group;
+        gp.raster_along_m = walk.along_m;
         if (g_opt_raster_dir.load(std::memory_order_relaxed) >= 0) gp.raster_along_m = uint32_t(g_opt_raster_dir.load());
-        gp.hint_a = hint_code(g_opt_hint_a.load(std::memory_order_relaxed));
-        gp.hint_b = hint_code(g_opt_hint_b.load(std::memory_order_relaxed));
+        gp.hint_a = hint_code(g_opt_hint_a.load(std::memory_order_relaxed) >= 0 ? g_opt_hint_a.load() : walk.hint_a);
+        gp.hint_b = hint_code(g_opt_hint_b.load(std::memory_order_relaxed) >= 0 ? g_opt_hint_b.load() : walk.hint_b);
         // block-scaled instruction descriptor: e4m3 x e4m3, UE8M0 scales (bit 23), N >> 3 at [17,23), M >> 4 at [24,29)
         gp.idesc = (1u << 23) | ((L.mx_bn >> 3) << 17) | (((128u * L.mx_cta) >> 4) << 24);
         gp.b_stage_bytes = (L.mx_bn / L.mx_cta) * 128;
@@ -890,9 +896,14 @@ static int launch_fp8(Fp8Launch& L, void* workspace, cudaStream_t stream) {
     fp.k_blocks = kb_total;
     fp.num_m_blocks = ceil_div(L.m, 128 * L.cta);
     fp.num_n_blocks = ceil_div(L.n, L.bn);
-    fp.raster_group = 8;
-    fp.raster_along_m = L.m > L.n ? 0 : 1;
-    fp.idesc = make_idesc(128 * L.cta, L.bn, 0u, 0, 0);
+    const WalkOrder walk_p = choose_walk(fp.num_m_blocks, fp.num_n_blocks, uint64_t(128) * L.cta * L.k, uint64_t(L.bn) * L.k,
+                                         L.m > L.n);
+    fp.raster_group = g_opt_raster.load(std::memory_order_relaxed) > 0 ? uint32_t(g_opt_raster.load()) : walk_p.group;
+    fp.raster_along_m = walk_p.along_m;
+    if (g_opt_raster_dir.load(std::memory_order_relaxed) >= 0) fp.raster_along_m = uint32_t(g_opt_raster_dir.load());
+    fp.hint_a = hint_code(g_opt_hint_a.load(std::memory_order_relaxed) >= 0 ? g_opt_hint_a.load() : walk_p.hint_a);
+    fp.hint_b = hint_code(g_opt_hint_b.load(std::memory_order_relaxed) >= 0 ? g_opt_hint_b.load() : walk_p.hint_b);
+    fp.idesc = make_idesc(128 * L.cta, L.bn / 2, 0u, 0, 0);   // one column half per instruction
     fp.sfa_ld = uint32_t(L.sfa_ld); fp.sfb_ld = uint32_t(L.sfb_ld);
     fp.sfb_rows = ceil_div(L.n, 128);
     fp.sfa = L.sfa; fp.sfb = L.sfb;

@@ -3,16 +3,23 @@
 // A [M,K] e4m3 with one fp32 scale per 1x128 strip, B [N,K] e4m3 with one fp32 scale per 128x128 block.
 // Not in the reference (BASELINE.json north_star item 1).  The scales are arbitrary fp32 values, so they
 // cannot ride in the instruction (kind::mxf8f6f4 block scaling wants UE8M0): every 128-wide K block is a
-// separate tcgen05 accumulation (kind::f8f6f4, fp32) into one of two TMEM buffers, and the promotion warps
-// pull it out (tcgen05.ld), multiply by sfa*sfb and add it to fp32 accumulators held in REGISTERS.
+// separate tcgen05 accumulation (kind::f8f6f4, fp32) into TMEM, and the promotion warps pull it out
+// (tcgen05.ld), multiply by sfa*sfb and add it to fp32 accumulators held in REGISTERS.
 //
 //   warp 0        : TMA producer          (A/B tiles -> smem ring, SWIZZLE_128B, 128 fp8 = 128 B per row)
-//   warp 1        : MMA issuer            (4 x K=32 MMAs per K block; commit -> ring slot + partial buffer)
+//   warp 1        : MMA issuer            (per K block and column half: 4 x K=32 MMAs, commit -> that half's barrier)
 //   warp 2        : TMEM alloc / dealloc
-//   warps 4..11   : promotion + epilogue  (2 warp groups; group g owns the 32-column chunks c = g, g+2, ...)
-// While the promotion of block kb runs from buffer kb&1, the tensor core fills the other buffer with
-// block kb+1; the final bf16 store of a tile overlaps the first K blocks of the next tile because the
-// running sums live in registers, not in TMEM.
+//   warps 4..11   : promotion + epilogue  (2 warp groups; group g owns the column half g of the tile)
+//
+// What paces it (measured, profiles/r02_tmem_ld_throughput.log and r02_fp8_promo_*): tcgen05.ld delivers 350-630
+// B/clk/SM (4-8 reader warps, MMAs running), so reading every accumulator once per K block (512 N bytes per
+// CTA) costs ~0.9 N clocks against 2 N clocks of fp8 MMAs - the TMEM read is NOT the ceiling round 1 took it for.
+// The chain MMA done -> barrier -> load -> release -> barrier -> next MMA into that buffer is: with two whole-tile
+// buffers it is ~600 clocks against 448 (N = 224) of MMAs.  So the tile is computed in two column HALVES with
+// their own TMEM buffers and barriers: four half buffers in flight, a half may be promoted while the tensor core
+// works through the three that follow it.  To make a half a contiguous run of output columns, B is staged per
+// CTA as two boxes of N/4 rows (columns [h N/2 + rank N/4, +N/4) for h = 0, 1): the half-h MMA (UMMA N = N/2)
+// then reads box h of both CTAs of the pair.
 #pragma once
 #include "gemm_sm100.cuh"
 
@@ -28,13 +35,14 @@ struct Fp8Params {
     uint32_t k_blocks;
     uint32_t num_m_blocks, num_n_blocks;
     uint32_t raster_group, raster_along_m;
-    uint32_t idesc;
+    uint32_t idesc;            // UMMA N = block_n / 2 (one column half per instruction)
     uint32_t sfa_ld, sfb_ld;   // row pitch of the scale tensors, in floats
     uint32_t sfb_rows;         // ceil(n / 128)
     const float* sfa;          // [m, ceil(k/128)]
     const float* sfb;          // [ceil(n/128), ceil(k/128)]
     const int32_t* gate;       // run only when *gate == gate_expect (nullptr: always)
     int32_t gate_expect;
+    uint64_t hint_a, hint_b;   // L2 eviction hints of the operand loads (0 = normal), see GemmParams
 };
 
 struct Fp8Smem {
@@ -53,7 +61,8 @@ __host__ __device__ inline Fp8Smem make_fp8_smem(uint32_t block_n, uint32_t cta,
     l.off_b = l.off_a + stages * l.a_stage_bytes;
     l.off_sfb = l.off_b + stages * l.b_stage_bytes;
     l.off_bar = l.off_sfb + 2 * 3 * l.sfb_pitch * 4;
-    l.total = l.off_bar + (2 * stages + 4) * 8 + 16;
+    // full[stages] empty[stages] part_full[2 buffers][2 halves] part_empty[2][2] + tmem ptr
+    l.total = l.off_bar + (2 * stages + 8) * 8 + 16;
     return l;
 }
 
@@ -61,7 +70,7 @@ __host__ __device__ inline Fp8Smem make_fp8_smem(uint32_t block_n, uint32_t cta,
 // group (4 K blocks of MMAs, ~2000 clocks) before first use, so the L2 round trip never sits in the promotion
 // chain.  (Round 1 fetched one float per K block two blocks ahead and rotated it through registers: the rotation
 // waited on the youngest load, every K block paid an L2 latency, and the kernel ran at 2500 clocks per K block
-// against 450 of MMAs: profiles/r02_fp8_promo_ncu_*.)
+// against 450 of MMAs.)
 __device__ __forceinline__ float4 load_scales4(const float* row, uint32_t kb, uint32_t k_blocks, bool vec) {
     if (vec && kb + 4 <= k_blocks) return __ldg(reinterpret_cast<const float4*>(row + kb));
     float4 v;
@@ -75,7 +84,7 @@ __device__ __forceinline__ float pick4(const float4& v, uint32_t i) {
     return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w;
 }
 
-__device__ __forceinline__ void stage_row_bf16(uint32_t stage_base, uint32_t row, const float (&v)[32]) {
+__device__ __forceinline__ void stage_row_bf16(uint32_t stage_base, uint32_t row, const float* v) {
     const uint32_t row_base = stage_base + row * 64;
     const uint32_t x = (row >> 1) & 3;
 #pragma unroll
@@ -92,14 +101,16 @@ template <int kCta, uint32_t kBN>
 __global__ void __launch_bounds__(kFp8Threads, 1)
 gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                       const __grid_constant__ CUtensorMap tm_d, const Fp8Params p) {
-    static_assert(kBN % 32 == 0 && kBN <= 256 && kBN % (16 * kCta) == 0, "unsupported block_n");
+    constexpr uint32_t kHalf = kBN / 2;              // columns per warp group, per MMA and per TMEM half buffer
+    constexpr uint32_t kBoxN = kBN / (2 * kCta);     // B rows per TMA box (two boxes per CTA and stage)
+    constexpr uint32_t kUnits = kHalf / 16;          // 16-column units of a half (a unit never straddles a scale block)
+    constexpr uint32_t kLoads = (kHalf + 31) / 32;   // TMEM loads per half: 32 columns each, the last one 16 when odd
+    static_assert(kBN <= 256 && kHalf % 16 == 0 && kBoxN % 8 == 0, "unsupported block_n");
     ptx::grid_dep_launch();
     if (p.gate != nullptr) {
         ptx::grid_dep_wait();     // the flag was written by a previous grid
         if (*p.gate != p.gate_expect) return;   // grid-uniform
     }
-    constexpr uint32_t kChunks = kBN / 32;
-    constexpr uint32_t kOwned = (kChunks + 1) / 2;   // chunks per warp group (group 1 may own one less)
     constexpr uint32_t kTmemCols = (2 * kBN <= 32) ? 32 : (2 * kBN <= 64) ? 64 : (2 * kBN <= 128) ? 128
                                    : (2 * kBN <= 256) ? 256 : 512;
 
@@ -120,9 +131,9 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
     const Fp8Smem L = make_fp8_smem(kBN, kCta, stages, k_blocks);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.off_bar);
     uint64_t* empty_bar = full_bar + stages;
-    uint64_t* part_full_bar = empty_bar + stages;    // [2] partial product of one K block is in TMEM
-    uint64_t* part_empty_bar = part_full_bar + 2;    // [2] promotion warps have read it
-    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(part_empty_bar + 2);
+    uint64_t* part_full_bar = empty_bar + stages;    // [buffer * 2 + half] partial product of one K block is in TMEM
+    uint64_t* part_empty_bar = part_full_bar + 4;    // [buffer * 2 + half] that half's promotion warps have read it
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(part_empty_bar + 4);
 
     if constexpr (kCta == 2) ptx::cluster_sync();
 
@@ -136,9 +147,9 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             ptx::mbar_init(&full_bar[s], kCta);
             ptx::mbar_init(&empty_bar[s], 1);
         }
-        for (uint32_t s = 0; s < 2; ++s) {
+        for (uint32_t s = 0; s < 4; ++s) {
             ptx::mbar_init(&part_full_bar[s], 1);
-            ptx::mbar_init(&part_empty_bar[s], kCta * 8);   // one elected arrive per promotion warp of the pair
+            ptx::mbar_init(&part_empty_bar[s], kCta * 4);   // one elected arrive per warp of the owning group, both CTAs
         }
         ptx::fence_mbar_init();
     }
@@ -148,18 +159,19 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
     ptx::grid_dep_wait();
-    constexpr uint32_t kLoadN = kBN / kCta;
 
     if (warp < 4) {
         ptx::setmaxnreg_dec<56>();
         if (warp == 0) {
             // ------------------------------------------------ TMA producer
+            const uint64_t hint_a = p.hint_a != 0 ? p.hint_a : ptx::kEvictNormal;
+            const uint64_t hint_b = p.hint_b != 0 ? p.hint_b : ptx::kEvictNormal;
             uint32_t stage = 0, phase = 0;
             for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters) {
                 uint32_t mb, nb;
                 tile_coords(p, t, mb, nb);
                 const int32_t m_idx = static_cast<int32_t>(mb * (kBlockM * kCta) + cta_rank * kBlockM);
-                const int32_t n_idx = static_cast<int32_t>(nb * kBN + cta_rank * kLoadN);
+                const int32_t n_idx = static_cast<int32_t>(nb * kBN + cta_rank * kBoxN);   // box of half 0; half 1: + kHalf
                 for (uint32_t kb = 0; kb < k_blocks; ++kb) {
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                     if (ptx::elect_one()) {
@@ -167,13 +179,17 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
                         uint8_t* sb = smem + L.off_b + stage * L.b_stage_bytes;
                         const int32_t k_idx = static_cast<int32_t>(kb * kFp8BlockK);
                         if constexpr (kCta == 2) {
-                            ptx::tma_load_2d_pair(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
-                            ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
+                            ptx::tma_load_2d_pair(&tm_a, &full_bar[stage], sa, k_idx, m_idx, hint_a);
+                            ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb, k_idx, n_idx, hint_b);
+                            ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb + kBoxN * 128, k_idx,
+                                                  n_idx + static_cast<int32_t>(kHalf), hint_b);
                             if (is_leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * (L.a_stage_bytes + L.b_stage_bytes));
                             else ptx::mbar_arrive_remote(&full_bar[stage], 0);
                         } else {
-                            ptx::tma_load_2d(&tm_a, &full_bar[stage], sa, k_idx, m_idx);
-                            ptx::tma_load_2d(&tm_b, &full_bar[stage], sb, k_idx, n_idx);
+                            ptx::tma_load_2d(&tm_a, &full_bar[stage], sa, k_idx, m_idx, hint_a);
+                            ptx::tma_load_2d(&tm_b, &full_bar[stage], sb, k_idx, n_idx, hint_b);
+                            ptx::tma_load_2d(&tm_b, &full_bar[stage], sb + kBoxN * 128, k_idx,
+                                             n_idx + static_cast<int32_t>(kHalf), hint_b);
                             ptx::mbar_arrive_expect_tx(&full_bar[stage], L.a_stage_bytes + L.b_stage_bytes);
                         }
                     }
@@ -191,24 +207,27 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             uint32_t stage = 0, phase = 0, pc = 0;   // pc: running K-block counter (selects the TMEM buffer)
             for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters) {
                 for (uint32_t kb = 0; kb < k_blocks; ++kb, ++pc) {
-                    const uint32_t buf = pc & 1;
-                    ptx::mbar_wait(&part_empty_bar[buf], ((pc >> 1) & 1) ^ 1);
+                    const uint32_t buf = pc & 1, par = (pc >> 1) & 1;
                     ptx::mbar_wait(&full_bar[stage], phase);
-                    ptx::tc_fence_after();
-                    if (ptx::elect_one()) {
-                        const uint32_t a_lo = a_lo0 + stage * a_step;
-                        const uint32_t b_lo = b_lo0 + stage * b_step;
-                        const uint32_t tmem_d = tmem_base + buf * kBN;
 #pragma unroll
-                        for (uint32_t k = 0; k < 4; ++k) {   // 4 x (K = 32 fp8 = 32 bytes) inside the 128 B atom
-                            const uint64_t a_desc = (static_cast<uint64_t>(hi) << 32) | (a_lo + k * 2);
-                            const uint64_t b_desc = (static_cast<uint64_t>(hi) << 32) | (b_lo + k * 2);
-                            ptx::mma_f8<kCta>(tmem_d, a_desc, b_desc, idesc, k != 0);
+                    for (uint32_t h = 0; h < 2; ++h) {
+                        ptx::mbar_wait(&part_empty_bar[buf * 2 + h], par ^ 1);
+                        ptx::tc_fence_after();
+                        if (ptx::elect_one()) {
+                            const uint32_t a_lo = a_lo0 + stage * a_step;
+                            const uint32_t b_lo = b_lo0 + stage * b_step + h * ((kBoxN * 128) >> 4);
+                            const uint32_t tmem_d = tmem_base + buf * kBN + h * kHalf;
+#pragma unroll
+                            for (uint32_t k = 0; k < 4; ++k) {   // 4 x (K = 32 fp8 = 32 bytes) inside the 128 B atom
+                                const uint64_t a_desc = (static_cast<uint64_t>(hi) << 32) | (a_lo + k * 2);
+                                const uint64_t b_desc = (static_cast<uint64_t>(hi) << 32) | (b_lo + k * 2);
+                                ptx::mma_f8<kCta>(tmem_d, a_desc, b_desc, idesc, k != 0);
+                            }
+                            ptx::mma_commit<kCta>(&part_full_bar[buf * 2 + h]);
+                            if (h == 1) ptx::mma_commit<kCta>(&empty_bar[stage]);
                         }
-                        ptx::mma_commit<kCta>(&empty_bar[stage]);
-                        ptx::mma_commit<kCta>(&part_full_bar[buf]);
+                        __syncwarp();
                     }
-                    __syncwarp();
                     if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
             }
@@ -216,7 +235,7 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
     } else {
         // ------------------------------------------------ promotion + epilogue (warps 4..11)
         ptx::setmaxnreg_inc<224>();
-        const uint32_t group = (warp - 4) >> 2;                  // warp group 0 / 1
+        const uint32_t group = (warp - 4) >> 2;                  // warp group == column half it owns
         const uint32_t quad = warp & 3;                          // TMEM lane quadrant this warp may read
         const uint32_t row = quad * 32 + lane;                   // accumulator row inside the CTA tile
         const uint32_t gtid = (threadIdx.x - 128) & 127;         // thread index inside the warp group (== row)
@@ -224,7 +243,7 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
         const uint32_t sbase0 = smem_base + L.off_d + group * 2 * L.d_stage_bytes;
         uint8_t* sptr0 = smem + L.off_d + group * 2 * L.d_stage_bytes;
         uint32_t pc = 0, sbuf = 0, tile_par = 0;
-        float acc[kOwned][32];
+        float acc[kHalf];
         // Weight scales of a tile: 3 rows x k_blocks floats, copied to shared memory by the 256 promotion threads;
         // the copy for tile i + 1 is issued before the stores of tile i and lands behind them.
         const uint32_t ptid = threadIdx.x - 128;
@@ -263,99 +282,128 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             ptx::named_bar_sync(3, 256);
         }
 
+        // loop invariants of the promotion chain: barrier addresses (the arrival goes to the leader CTA's barrier),
+        // TMEM addresses of this group's half in both buffers
+        uint32_t pf_addr[2], pe_addr[2], taddr[2];
+#pragma unroll
+        for (uint32_t b = 0; b < 2; ++b) {
+            pf_addr[b] = ptx::smem_u32(&part_full_bar[b * 2 + group]);
+            pe_addr[b] = ptx::smem_u32(&part_empty_bar[b * 2 + group]);
+            if constexpr (kCta == 2) pe_addr[b] = ptx::mapa(pe_addr[b], 0);
+            taddr[b] = tmem_base + ((quad * 32) << 16) + b * kBN + group * kHalf;
+        }
+
         for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters, tile_par ^= 1) {
             uint32_t mb, nb;
             tile_coords(p, t, mb, nb);
             const uint32_t m0 = mb * (kBlockM * kCta) + cta_rank * kBlockM;
             const uint32_t n0 = nb * kBN;
+            const uint32_t c0 = n0 + group * kHalf;              // first output column of this group's half
             const float* sfa_row = p.sfa + static_cast<uint64_t>(min(m0 + row, p.m - 1)) * p.sfa_ld;
-            // the tile's columns touch at most three 128-wide scale blocks
-            const uint32_t nblk0 = n0 >> 7;
-            const float* sfb_t = sfb_s + tile_par * 3 * L.sfb_pitch;
+            // A half is at most 128 columns wide and starts on a multiple of 16: it touches at most two 128-column
+            // scale blocks, A (its first column's) and B (the next).  16-column unit u takes A's scale while
+            // u < units_a, B's after; as a bit mask per unit so that the choice is one LOP3 per K block.
+            const float* sfb_a = sfb_s + (tile_par * 3 + ((c0 >> 7) - (n0 >> 7))) * L.sfb_pitch;
+            const float* sfb_b = sfb_a + ((((c0 + kHalf - 1) >> 7) != (c0 >> 7)) ? L.sfb_pitch : 0u);
+            const uint32_t units_a = (128u - (c0 & 127u)) >> 4;
+            uint32_t take_a[kUnits];
 #pragma unroll
-            for (uint32_t ci = 0; ci < kOwned; ++ci)
+            for (uint32_t u = 0; u < kUnits; ++u) take_a[u] = u < units_a ? 0xFFFFFFFFu : 0u;
 #pragma unroll
-                for (uint32_t j = 0; j < 32; ++j) acc[ci][j] = 0.f;
+            for (uint32_t j = 0; j < kHalf; ++j) acc[j] = 0.f;
 
-            // this row's activation scales of K blocks [4g, 4g + 4) are in registers while group g runs; group g + 1
-            // is in flight
-            const bool vec = (reinterpret_cast<uintptr_t>(p.sfa) & 15) == 0 && (p.sfa_ld & 3) == 0;
-            float4 sa4 = load_scales4(sfa_row, 0, k_blocks, vec);
-            float4 sa4n = sa4;
-
-            for (uint32_t kb = 0; kb < k_blocks; ++kb, ++pc) {
-                const uint32_t ki = kb & 3;
-                if (ki == 0) {
-                    if (kb != 0) sa4 = sa4n;
-                    if (kb + 4 < k_blocks) sa4n = load_scales4(sfa_row, kb + 4, k_blocks, vec);
-                }
-                const float sa_c = pick4(sa4, ki);
-                const float s0 = sa_c * sfb_t[kb], s1 = sa_c * sfb_t[L.sfb_pitch + kb], s2 = sa_c * sfb_t[2 * L.sfb_pitch + kb];
-                const uint32_t buf = pc & 1;
-                ptx::mbar_wait(&part_full_bar[buf], (pc >> 1) & 1);
+            // One K block: fold this group's half of the partial product into the running sums.  kBuf is a literal
+            // in every call below (the loop is unrolled by four), sa the row's activation scale of this block.
+            auto promote = [&](uint32_t kb, uint32_t buf, uint32_t par, float sa) __attribute__((always_inline)) {
+                const float pa = sa * sfb_a[kb], pb = sa * sfb_b[kb];
+                float s[kUnits];
+#pragma unroll
+                for (uint32_t u = 0; u < kUnits; ++u)
+                    s[u] = __uint_as_float((take_a[u] & __float_as_uint(pa)) | (~take_a[u] & __float_as_uint(pb)));
+                ptx::mbar_wait_addr(pf_addr[buf], par);
                 ptx::tc_fence_after();
-                const uint32_t taddr = tmem_base + ((quad * 32) << 16) + buf * kBN;
                 uint32_t va[32], vb[32];
-                ptx::tmem_ld_32x32(taddr + group * 32, va);
+                ptx::tmem_ld_32x32(taddr[buf], va);
 #pragma unroll
-                for (uint32_t ci = 0; ci < kOwned; ++ci) {
-                    const uint32_t c = group + 2 * ci;           // this group's ci-th chunk
-                    if (c < kChunks) {
-                        ptx::tmem_ld_wait();
-                        // next chunk's load flies while this chunk is folded in
-                        const bool more = (ci + 1 < kOwned) && (c + 2 < kChunks);
-                        if (more) {
-                            if (ci & 1) ptx::tmem_ld_32x32(taddr + (c + 2) * 32, va);
-                            else ptx::tmem_ld_32x32(taddr + (c + 2) * 32, vb);
-                        } else {
-                            // every chunk of this buffer is in registers: hand it back to the tensor core
-                            ptx::tc_fence_before();
-                            __syncwarp();
-                            if (ptx::elect_one()) {
-                                if constexpr (kCta == 2) ptx::mbar_arrive_remote(&part_empty_bar[buf], 0);
-                                else ptx::mbar_arrive(&part_empty_bar[buf]);
-                            }
-                        }
-                        const uint32_t which = ((n0 + c * 32) >> 7) - nblk0;
-                        const float s = which == 0 ? s0 : which == 1 ? s1 : s2;
-                        if (ci & 1) {
-#pragma unroll
-                            for (uint32_t j = 0; j < 32; j += 2)
-                                ptx::fma2(acc[ci][j], acc[ci][j + 1], __uint_as_float(vb[j]), __uint_as_float(vb[j + 1]), s);
-                        } else {
-#pragma unroll
-                            for (uint32_t j = 0; j < 32; j += 2)
-                                ptx::fma2(acc[ci][j], acc[ci][j + 1], __uint_as_float(va[j]), __uint_as_float(va[j + 1]), s);
+                for (uint32_t i = 0; i < kLoads; ++i) {
+                    ptx::tmem_ld_wait();
+                    // the next load flies while this one is folded in
+                    if (i + 1 < kLoads) {
+                        uint32_t(&nxt)[32] = (i & 1) ? va : vb;
+                        if (32 * (i + 2) <= kHalf) ptx::tmem_ld_32x32(taddr[buf] + 32 * (i + 1), nxt);
+                        else ptx::tmem_ld_32x16(taddr[buf] + 32 * (i + 1), *reinterpret_cast<uint32_t(*)[16]>(&nxt[0]));
+                    } else {
+                        // the whole half is in registers: hand its TMEM buffer back to the tensor core
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (ptx::elect_one()) {
+                            if constexpr (kCta == 2) ptx::mbar_arrive_cluster_addr(pe_addr[buf]);
+                            else ptx::mbar_arrive_addr(pe_addr[buf]);
                         }
                     }
+                    const uint32_t(&cur)[32] = (i & 1) ? vb : va;
+#pragma unroll
+                    for (uint32_t j = 0; j < 32; j += 2) {
+                        if (32 * i + j < kHalf)
+                            ptx::fma2(acc[32 * i + j], acc[32 * i + j + 1], __uint_as_float(cur[j]), __uint_as_float(cur[j + 1]),
+                                      s[(32 * i + j) / 16]);
+                    }
+                }
+            };
+
+            // this row's activation scales of K blocks [4g, 4g + 4) are in registers while group g runs; group g + 1
+            // is in flight.  pc counts K blocks over the whole kernel: buffer = pc & 1, barrier parity = (pc >> 1) & 1.
+            const bool vec = (reinterpret_cast<uintptr_t>(p.sfa) & 15) == 0 && (p.sfa_ld & 3) == 0;
+            float4 sa4n = load_scales4(sfa_row, 0, k_blocks, vec);
+            uint32_t kb = 0;
+            for (; kb + 4 <= k_blocks; kb += 4, pc += 4) {
+                const float4 sa4 = sa4n;
+                if (kb + 4 < k_blocks) sa4n = load_scales4(sfa_row, kb + 4, k_blocks, vec);
+                const uint32_t b0 = pc & 1, par0 = (pc >> 1) & 1;
+                if (b0 == 0) {
+                    promote(kb, 0, par0, sa4.x);
+                    promote(kb + 1, 1, par0, sa4.y);
+                    promote(kb + 2, 0, par0 ^ 1, sa4.z);
+                    promote(kb + 3, 1, par0 ^ 1, sa4.w);
+                } else {
+                    promote(kb, 1, par0, sa4.x);
+                    promote(kb + 1, 0, par0 ^ 1, sa4.y);
+                    promote(kb + 2, 1, par0 ^ 1, sa4.z);
+                    promote(kb + 3, 0, par0, sa4.w);
                 }
             }
+            for (uint32_t i = 0; kb < k_blocks; ++kb, ++pc, ++i) {   // K not a multiple of 512
+                const float sa = pick4(sa4n, i);
+                if ((pc & 1) == 0) promote(kb, 0, (pc >> 1) & 1, sa);
+                else promote(kb, 1, (pc >> 1) & 1, sa);
+            }
 
-            // ---- tile done: registers -> bf16 -> swizzled smem -> TMA store (per warp group)
+            // ---- tile done: registers -> bf16 -> swizzled smem -> TMA store (per warp group, 32-column boxes; when
+            // the half is an odd multiple of 16 wide the last box is moved back by 16 columns and rewrites them)
             const uint32_t t_next = t + num_clusters;
             float sfb_next[kSfbPer];
             if (t_next < num_tiles) sfb_load(t_next, 0, sfb_next);
 #pragma unroll
-            for (uint32_t ci = 0; ci < kOwned; ++ci) {
-                const uint32_t c = group + 2 * ci;
-                if (c < kChunks && n0 + c * 32 < p.n) {
+            for (uint32_t i = 0; i < kLoads; ++i) {
+                const uint32_t col = (32 * (i + 1) <= kHalf) ? 32 * i : kHalf - 32;   // inside the half
+                if (c0 + col < p.n) {
                     if (gtid == 0) ptx::tma_store_wait_read<1>();
                     ptx::named_bar_sync(bar_id, 128);
-                    stage_row_bf16(sbase0 + sbuf * L.d_stage_bytes, row, acc[ci]);
+                    stage_row_bf16(sbase0 + sbuf * L.d_stage_bytes, row, &acc[col]);
                     ptx::fence_async_smem();
                     ptx::named_bar_sync(bar_id, 128);
                     if (gtid == 0) {
                         if (m0 < p.m)
                             ptx::tma_store_2d(&tm_d, sptr0 + sbuf * L.d_stage_bytes,
-                                              static_cast<int32_t>(n0 + c * 32), static_cast<int32_t>(m0));
+                                              static_cast<int32_t>(c0 + col), static_cast<int32_t>(m0));
                         ptx::tma_store_commit();
                     }
                     sbuf ^= 1;
                 }
             }
             if (t_next < num_tiles) {
-                // every promotion thread is past its last read of this tile's scales' predecessor buffer: the MMA
-                // of the next tile's first K block cannot have been promoted before this point either
+                // nobody reads buffer tile_par ^ 1 during this tile; the barrier below orders these stores before
+                // the first read of the next tile
                 sfb_store(tile_par ^ 1, 0, sfb_next);
                 for (uint32_t base = 256 * kSfbPer; base < sfb_total; base += 256 * kSfbPer) {
                     float v[kSfbPer];

@@ -172,6 +172,39 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 #endif
 }
 
+// Address-based variants for hot loops: the 32-bit shared-memory address is computed once outside the loop (the
+// generic-pointer forms above re-derive it, and the CTA's window base, on every call when registers are tight),
+// and the watchdog traps without formatting a message (no stack frame, no call in the loop).
+__device__ __forceinline__ bool mbar_try_wait_addr(uint32_t bar_addr, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t"
+        "}\n"
+        : "=r"(ok) : "r"(bar_addr), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_addr(uint32_t bar_addr, uint32_t parity) {
+    if (mbar_try_wait_addr(bar_addr, parity)) return;
+#if DGA_WATCHDOG_SPINS
+    const unsigned long long t0 = globaltimer();
+    while (!mbar_try_wait_addr(bar_addr, parity)) {
+        if (globaltimer() - t0 > 4000000000ull) __trap();
+    }
+#else
+    while (!mbar_try_wait_addr(bar_addr, parity)) {}
+#endif
+}
+__device__ __forceinline__ void mbar_arrive_addr(uint32_t bar_addr) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar_addr) : "memory");
+}
+// `cluster_addr`: mapa() of the barrier's address into the target CTA, computed once.
+__device__ __forceinline__ void mbar_arrive_cluster_addr(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" :: "r"(cluster_addr) : "memory");
+}
+
 // --------------------------------------------------------------------- TMA
 __device__ __forceinline__ void prefetch_tensormap(const void* desc) {
     asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(desc)) : "memory");

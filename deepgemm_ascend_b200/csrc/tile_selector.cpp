@@ -157,6 +157,31 @@ bool aligned16(uint64_t elems, uint32_t bytes) { return (elems * bytes) % 16 == 
 
 }  // namespace
 
+// Walk order for problems whose operands do not fit L2 together.  The ~74 tiles in flight cover `group` blocks of
+// one dimension x the rest of the wave along the other.  The panels (block rows x K) of the grouped dimension
+// stay resident across the waves of a group; every panel of the other operand is shared by the `group` tiles
+// that use it at the same moment and is never touched again inside the group, so it is loaded evict-first and
+// cannot push the resident set out.  Measured on fp8 config 4 (profiles/r02_fp8_raster_sweep.log): the resident
+// set holds while it stays near 32 MB (the 126 MB L2 is two halves, and lines read from both dies live in both) -
+// groups of 8 row blocks with evict-first weights: 373 MB of DRAM traffic against 620 MB for the round-1 walk
+// (algorithmic 245 MB); 16 row blocks (64 MB resident) is back at 600 MB.
+WalkOrder choose_walk(uint32_t m_blocks, uint32_t n_blocks, uint64_t panel_a_bytes, uint64_t panel_b_bytes, bool m_gt_n) {
+    WalkOrder w{8, m_gt_n ? 0u : 1u, 0, 0};   // tiling_params.h:63-64: direction from m > n, fixed group
+    const uint64_t a_total = panel_a_bytes * m_blocks, b_total = panel_b_bytes * n_blocks;
+    const uint64_t resident = 32ull << 20;
+    if (a_total + b_total <= (96ull << 20)) return w;   // both operands stay in L2 whatever the order
+    auto group_for = [&](uint64_t panel, uint32_t blocks) {
+        return uint32_t(std::max<uint64_t>(1, std::min<uint64_t>(blocks, resident / std::max<uint64_t>(panel, 1))));
+    };
+    const uint32_t g0 = group_for(panel_a_bytes, m_blocks), g1 = group_for(panel_b_bytes, n_blocks);
+    const uint64_t traffic0 = a_total + b_total * ceil_div(m_blocks, g0);   // groups of row blocks, weights stream
+    const uint64_t traffic1 = b_total + a_total * ceil_div(n_blocks, g1);   // groups of column blocks, activations stream
+    if (traffic0 <= traffic1) w = WalkOrder{g0, 0, 0, 1};
+    else w = WalkOrder{g1, 1, 1, 0};
+    w.group = std::min<uint32_t>(w.group, 255);
+    return w;
+}
+
 uint32_t clusters_of_four() {
     // clusters of 4 CTAs that fit beside each other with the persistent kernel's footprint (one CTA per SM): 33 on a
     // B200 (132 of 148 SMs: a cluster lives inside one GPC; tools/probes/cluster_occupancy.cu)

@@ -44,6 +44,13 @@ int select_kernel(DgaTilingPlan& plan);
 int finalize_plan(DgaTilingPlan& plan);
 int select_kernel_with_cache(DgaTilingPlan& plan);
 
+// Rasterisation of the persistent kernels (role of swizzleOffset / swizzleDirection, tiling_params.h:63-64) chosen
+// from the bytes of one block row / block column panel (rows x K) and the L2 size; hints: 0 normal, 1 evict-first.
+struct WalkOrder {
+    uint32_t group, along_m, hint_a, hint_b;
+};
+WalkOrder choose_walk(uint32_t m_blocks, uint32_t n_blocks, uint64_t panel_a_bytes, uint64_t panel_b_bytes, bool m_gt_n);
+
 // Clusters of four CTAs (clusterShape 4) the device places side by side at one CTA per SM.
 uint32_t clusters_of_four();
 

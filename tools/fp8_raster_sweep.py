@@ -43,6 +43,29 @@ def main():
     torch.cuda.synchronize()
     assert ex[0].path() == "block_scaled"
     ref = c[0].clone()
+    if mode == "ab":
+        # a few candidates, interleaved over several rounds: single passes drift with the power-capped clock
+        cands = [(1, 8, 0, 0), (1, 2, 0, 0), (0, 8, 0, 1), (0, 8, 2, 1), (1, 8, 1, 2), (0, 8, 0, 0), (1, 11, 1, 2)]
+        total = {c: 0.0 for c in cands}
+        rounds = 8
+        for _ in range(rounds):
+            for cand in cands:
+                for key, val in zip(("raster_along_m", "raster_group", "hint_a", "hint_b"), cand):
+                    dga.set_option(key, val)
+                for i in range(3):
+                    ex[i % sets]()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for i in range(20):
+                    ex[i % sets]()
+                e1.record()
+                torch.cuda.synchronize()
+                total[cand] += e0.elapsed_time(e1) * 50.0
+        for cand in cands:
+            us = total[cand] / rounds
+            print("dir=%d group=%2d hint_a=%d hint_b=%d: %7.1f us  %6.1f TFLOP/s (mean of %d interleaved rounds x 20)" % (
+                cand + (us, 2.0 * m * n * k / us / 1e6, rounds)), flush=True)
+        return
     for cfg in configs():
         for key, val in cfg.items():
             dga.set_option(key, val)
