@@ -22,6 +22,16 @@ HINTS = ((0, 0), (1, 2), (2, 1), (0, 2), (2, 0), (1, 0), (0, 1))
 
 
 def configs():
+    if os.environ.get("SWEEP_ONE"):   # "dir,group,hint_a,hint_b": one configuration per process (evict-last lines of an
+        d, g, ha, hb = (int(v) for v in os.environ["SWEEP_ONE"].split(","))   # earlier configuration survive in L2)
+        yield {"raster_along_m": d, "raster_group": g, "hint_a": ha, "hint_b": hb}
+        return
+    if os.environ.get("SWEEP_SHORT"):
+        yield {"raster_along_m": -1, "raster_group": -1, "hint_a": -1, "hint_b": -1}     # the library's own rule
+        yield {"raster_along_m": 0, "raster_group": 8, "hint_a": 0, "hint_b": 1}
+        yield {"raster_along_m": 1, "raster_group": 8, "hint_a": 0, "hint_b": 0}
+        yield {"raster_along_m": -1, "raster_group": -1, "hint_a": -1, "hint_b": -1}
+        return
     for d, g, (ha, hb) in itertools.product(DIRS, GROUPS, HINTS):
         yield {"raster_along_m": d, "raster_group": g, "hint_a": ha, "hint_b": hb}
 
