@@ -149,11 +149,13 @@ _GOLDEN_INPUTS = {}   # inputs of the last sample (generated once per run, not p
 def cpu_golden_run(shape, budget_s, max_reps):
     """The reference's CPU golden for this path: np.matmul of the fp16 inputs widened to fp32
     (deep_gemm_ascend/scripts/gen_golden.py:14-15), restated in oracle.matmul_oracle.golden_fp32, on all host cores.
-    The whole problem when one repetition is <= 150 GFLOP (config 2: all 4096 rows, ~0.13 s); beyond that a bounded
-    sample: M is cut so that one repetition is ~60 GFLOP over the full N and K. Repeated until the budget is used."""
+    The whole problem when one repetition is <= 1.5 TFLOP (config 2: all 4096 rows, ~0.13 s); beyond that a bounded
+    sample: M is cut (to a multiple of 128 rows) so that one repetition is ~1.2 TFLOP over the full N and K (config 5:
+    1408 of 16384 rows, 1-2 s; a thinner slab would time the fp16 -> fp32 widening of the 822 MB weight, not the
+    GEMM). Repeated until the budget is used."""
     from oracle import matmul_oracle as orc
     m, n, k = shape["m"], shape["n_total"] if shape["scaling"] == "strong" else shape["n"], shape["k"]
-    rows = m if 2.0 * m * n * k <= 150e9 else max(1, min(m, int(60e9 / (2.0 * n * k))))
+    rows = m if 2.0 * m * n * k <= 1.5e12 else max(1, min(m, int(1.2e12 / (2.0 * n * k)) // 128 * 128))
     if _GOLDEN_INPUTS.get("key") != (rows, n, k):
         rng = np.random.RandomState(0)
         _GOLDEN_INPUTS.update(key=(rows, n, k), x1=rng.uniform(1, 10, [rows, k]).astype(np.float16),

@@ -13,7 +13,8 @@ ACL_FORMAT_ND = 2
 ACLNN_SUCCESS = 0
 
 KERNEL_COMMON, KERNEL_SMALL, KERNEL_PADDING_COMMON, KERNEL_SPLITK, KERNEL_STREAMK = 0, 1, 2, 3, 4
-KERNEL_NAMES = {0: "Common", 1: "Small", 2: "PaddingCommon", 3: "SplitK", 4: "StreamK"}
+KERNEL_SPLITK_REDUCE, KERNEL_CLUSTER_SPLITK = 5, 6
+KERNEL_NAMES = {0: "Common", 1: "Small", 2: "PaddingCommon", 3: "SplitK", 4: "StreamK", 5: "SplitKReduce", 6: "ClusterSplitK"}
 
 
 class AclTensor(ctypes.Structure):

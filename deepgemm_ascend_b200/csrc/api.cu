@@ -282,20 +282,22 @@ static int launch_jit(const DenseLaunch& L, const GemmParams& gp, cudaStream_t s
     return ACLNN_SUCCESS;
 }
 
-template <int kCta, typename OutT, bool kBMn, int kMode = kModePlain, bool kSk = false, bool kMc = false>
+template <int kCta, typename OutT, bool kBMn, int kMode = kModePlain, bool kSk = false, bool kMc = false, bool kKs = false>
 static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaStream_t stream) {
-    if constexpr (kMode == kModePlain && !kSk && !kMc) {
+    if constexpr (kMode == kModePlain && !kSk && !kMc && !kKs) {
         // a stream-K plan whose remainder came out empty is the plain walk
         if (gp.sk_tiles != 0) return launch_common_inst<kCta, OutT, kBMn, kMode, true>(L, gp, stream);
         // two CTA pairs per cluster, A multicast between them (16-bit outputs over either weight layout)
         if constexpr (kCta == 2 && sizeof(OutT) == 2) {
+            if (L.plan.kernelSerial == DGA_KERNEL_CLUSTER_SPLITK)
+                return launch_common_inst<kCta, OutT, kBMn, kMode, false, false, true>(L, gp, stream);
             if (L.plan.clusterShape == 4) return launch_common_inst<kCta, OutT, kBMn, kMode, false, true>(L, gp, stream);
         }
     }
-    if constexpr ((kMode == kModePlain || kMode == kModeBatched || kMode == kModeSplitK) && !kSk && !kMc) {
+    if constexpr ((kMode == kModePlain || kMode == kModeBatched || kMode == kModeSplitK) && !kSk && !kMc && !kKs) {
         if (jit_enabled() && L.num_peers == 0) return launch_jit(L, gp, stream, kMode);
     }
-    auto kernel = gemm_sm100_kernel<kCta, OutT, kBMn, false, kMode, kSk, kMc>;
+    auto kernel = gemm_sm100_kernel<kCta, OutT, kBMn, false, kMode, kSk, kMc, kKs>;
     int rc = set_smem_attr(kernel, L.plan.smemBytes);
     if (rc != ACLNN_SUCCESS) return rc;
     cudaLaunchConfig_t cfg{};
@@ -304,7 +306,7 @@ static int launch_common_inst(const DenseLaunch& L, const GemmParams& gp, cudaSt
     cfg.dynamicSmemBytes = L.plan.smemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
-    fill_launch_attrs(cfg, attr, kMc ? 4 : kCta, /*co_resident=*/kSk);
+    fill_launch_attrs(cfg, attr, (kMc || kKs) ? 4 : kCta, /*co_resident=*/kSk);
     DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, L.tm_a, L.tm_b, L.peers, gp));  // no scale maps here
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
@@ -360,7 +362,8 @@ static int encode_common(DenseLaunch& L) {
                             CU_TENSOR_MAP_SWIZZLE_128B);
     }
     // clusterShape 4: every CTA fetches half of its 128 A rows and receives the other half from its twin
-    int rc = make_tmap_2d(&L.tm_a, L.eff.a, p.dtype, p.k, p.m, L.eff.lda, 64, p.clusterShape == 4 ? 64 : 128,
+    const bool multicast_a = p.clusterShape == 4 && p.kernelSerial != DGA_KERNEL_CLUSTER_SPLITK;
+    int rc = make_tmap_2d(&L.tm_a, L.eff.a, p.dtype, p.k, p.m, L.eff.lda, 64, multicast_a ? 64 : 128,
                           CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != ACLNN_SUCCESS) return rc;
     if (p.layoutTagB == 1)  // weight stored [N, K]
@@ -405,7 +408,8 @@ static void common_params(const DgaTilingPlan& p, GemmParams& gp) {
     gp.k_blocks = ceil_div(p.k, 64);
     gp.num_m_blocks = ceil_div(p.m, 128 * cta);
     gp.num_n_blocks = ceil_div(p.n, p.n1);
-    if (p.clusterShape == 4) gp.num_n_blocks /= 2;   // the cluster walks pairs of N tiles (finalize_plan: even count)
+    if (p.clusterShape == 4 && p.kernelSerial != DGA_KERNEL_CLUSTER_SPLITK)
+        gp.num_n_blocks /= 2;   // the cluster walks pairs of N tiles (finalize_plan: even count)
     gp.raster_group = p.swizzleOffset;
     if (g_opt_raster.load(std::memory_order_relaxed) > 0) gp.raster_group = uint32_t(g_opt_raster.load());
     gp.raster_along_m = p.swizzleDirection;
@@ -576,6 +580,7 @@ static int launch_variant(DenseLaunch& L, cudaStream_t stream, void* workspace) 
     switch (L.plan.kernelSerial) {
         case DGA_KERNEL_COMMON:
         case DGA_KERNEL_SMALL:
+        case DGA_KERNEL_CLUSTER_SPLITK:
         case DGA_KERNEL_PADDING_COMMON: return launch_common(L, stream, nullptr);
         case DGA_KERNEL_STREAMK:
         case DGA_KERNEL_SPLITK_REDUCE:

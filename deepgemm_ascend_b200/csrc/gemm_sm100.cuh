@@ -280,7 +280,16 @@ __device__ __forceinline__ void resolve_item(const GemmParams& p, WorkItem& w, u
 // bytes leave L2 per flop.  A stage may be refilled once BOTH pairs have consumed it: every leader's commit goes
 // to the empty barrier of all four CTAs (count 2).  Everything behind the ring (TMEM, epilogue) stays per pair.
 // num_n_blocks then counts 2 * block_n wide column groups; the host only takes it for an even number of N tiles.
-template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain, bool kSk = false, bool kMc = false>
+// kKs (DGA_KERNEL_CLUSTER_SPLITK; the reference's answer to "tiles << cores" is stream-K + ReduceAdd through the
+// workspace, padding_streamk_matmul_kernel.h:33-108): a cluster of FOUR CTAs = two cta_group::2 pairs on the SAME
+// 256 x n1 tile, each pair accumulating one half of K.  Afterwards CTA (pair p, rank q) owns column half p of its 128
+// rows: it stages the other half of its fp32 accumulator in its (drained) ring, ships it with one bulk DSMEM copy
+// into the ring of its twin (pair 1 - p, rank q), adds the half it receives to its own and stores.  No workspace, no
+// second launch, no flags in global memory; one tile per cluster (the rings are busy after the main loop).  For
+// shapes whose wide tiles fill under half of the machine: the wide tile keeps the operand bytes per flop that one
+// SM can ingest (64 B/clk), the K split fills the SMs.
+template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain, bool kSk = false, bool kMc = false,
+          bool kKs = false>
 __device__ __forceinline__ void
 gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensorMap& tm_d, const CUtensorMap& tm_sfa,
                 const CUtensorMap& tm_sfb, const PeerMaps& peers, const GemmParams& p) {
@@ -290,6 +299,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
     static_assert(kMode != kModeSplitK || (sizeof(OutT) == 4 && !kMx), "split-K slices leave fp32 partial tiles");
     static_assert(!kSk || (kMode == kModePlain && !kMx), "stream-K is a variant of the plain 16-bit kernel");
     static_assert(!kMc || (kCta == 2 && kMode == kModePlain && !kSk && !kMx), "the multicast cluster is two whole-tile 16-bit CTA pairs");
+    static_assert(!kKs || (kCta == 2 && kMode == kModePlain && !kSk && !kMx && !kMc), "the K-split cluster is two 16-bit CTA pairs on one tile");
     ptx::grid_dep_launch();   // the next grid on the stream may set itself up while this one runs
     const bool tracing = (p.debug & 16) != 0 && p.trace != nullptr;
     if (tracing && threadIdx.x == 0) {
@@ -306,10 +316,11 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
 
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lane = threadIdx.x & 31;
-    constexpr uint32_t kClusterCtas = kMc ? 4 : kCta;
+    constexpr bool kQuad = kMc || kKs;                         // clusters of four CTAs = two pairs
+    constexpr uint32_t kClusterCtas = kQuad ? 4 : kCta;
     const uint32_t cluster_rank = (kCta == 2) ? ptx::cluster_ctarank() : 0u;
-    const uint32_t pair = kMc ? cluster_rank >> 1 : 0u;        // which of the cluster's CTA pairs (N neighbour)
-    const uint32_t cta_rank = kMc ? cluster_rank & 1u : cluster_rank;   // rank inside the pair
+    const uint32_t pair = kQuad ? cluster_rank >> 1 : 0u;      // which of the cluster's CTA pairs (kMc: N neighbour, kKs: K half)
+    const uint32_t cta_rank = kQuad ? cluster_rank & 1u : cluster_rank;   // rank inside the pair
     const uint32_t leader_rank = pair * 2;                     // cluster rank of this pair's MMA-issuing CTA
     const bool is_leader = cta_rank == 0;
     const uint32_t num_clusters = gridDim.x / kClusterCtas;
@@ -323,6 +334,10 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
     uint64_t* tmem_full_bar = empty_bar + stages;
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+    // kKs: the exchange barriers sit where the second accumulator stage's would (one tile per cluster: stage 1 is never
+    // used).  xchg_ready: the twin's ring is drained and its receive barrier armed; xchg_recv: the twin's half has landed.
+    uint64_t* xchg_ready_bar = &tmem_full_bar[1];
+    uint64_t* xchg_recv_bar = &tmem_empty_bar[1];
 
     if constexpr (kCta == 2) ptx::cluster_sync();  // peer must be resident before cta_group::2 alloc
 
@@ -340,9 +355,13 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             ptx::mbar_init(&full_bar[s], kCta);  // leader expect_tx arrive (+ peer's remote arrive)
             ptx::mbar_init(&empty_bar[s], kMc ? 2 : 1);   // one tcgen05.commit per pair that reads the stage (multicast)
         }
-        for (uint32_t s = 0; s < 2; ++s) {
+        for (uint32_t s = 0; s < (kKs ? 1u : 2u); ++s) {
             ptx::mbar_init(&tmem_full_bar[s], 1);
             ptx::mbar_init(&tmem_empty_bar[s], kCta * 128);  // every epilogue thread of the pair
+        }
+        if constexpr (kKs) {
+            ptx::mbar_init(xchg_ready_bar, 1);
+            ptx::mbar_init(xchg_recv_bar, 1);
         }
         ptx::fence_mbar_init();
     }
@@ -370,6 +389,10 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             int32_t z = static_cast<int32_t>(slab);   // third tensor-map coordinate: batch entry (mode 1) or group (mode 2)
             tile_coords(p, w.tile, mb, nb);
             if constexpr (kMc) nb = nb * 2 + pair;
+            if constexpr (kKs) {   // this pair's half of the K blocks
+                w.kb0 = pair * (p.k_blocks / 2);
+                w.kb1 = pair == 0 ? p.k_blocks / 2 : p.k_blocks;
+            }
             const int32_t m_idx = static_cast<int32_t>(mb * (kBlockM * kCta) + cta_rank * kBlockM);
             const int32_t n_idx = static_cast<int32_t>(nb * p.block_n + cta_rank * load_n);
             if constexpr (kMode == kModeMGrouped) {
@@ -475,6 +498,10 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                     const int32_t g = __ldg(p.group_index + (kMode == kModeMasked ? slab_of_item : mb * kBlockM));
                     if (kMode == kModeMasked ? static_cast<int32_t>(mb * kBlockM) >= g : g < 0) { --iter; continue; }
                 }
+                if constexpr (kKs) {
+                    w.kb0 = pair * (p.k_blocks / 2);
+                    w.kb1 = pair == 0 ? p.k_blocks / 2 : p.k_blocks;
+                }
                 const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
                 ptx::mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
                 ptx::tc_fence_after();
@@ -511,6 +538,10 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                         }
                         if constexpr (kMc) {
                             ptx::mma_commit_multicast<kCta>(&empty_bar[stage], 0xF);
+                            if (kb + 1 == k_blocks)
+                                ptx::mma_commit_multicast<kCta>(&tmem_full_bar[as], static_cast<uint16_t>(0x3u << leader_rank));
+                        } else if constexpr (kKs) {   // this pair's two CTAs (ranks 2 pair, 2 pair + 1)
+                            ptx::mma_commit_multicast<kCta>(&empty_bar[stage], static_cast<uint16_t>(0x3u << leader_rank));
                             if (kb + 1 == k_blocks)
                                 ptx::mma_commit_multicast<kCta>(&tmem_full_bar[as], static_cast<uint16_t>(0x3u << leader_rank));
                         } else {
@@ -551,9 +582,13 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                         ptx::tma_store_3d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes, c0, static_cast<int32_t>(m0), zb);
                     else
                         ptx::tma_store_2d(&tm_d, smem + L.off_d + buf * L.d_stage_bytes, c0, static_cast<int32_t>(m0));
-                    for (uint32_t i = 0; i < p.num_peers; ++i)   // same chunk into every peer's C (NVLink)
-                        ptx::tma_store_2d(&peers.m[i], smem + L.off_d + buf * L.d_stage_bytes, c0,
+                    // same chunk into every peer's C (NVLink); the CTAs start their round at different peers so
+                    // that at any moment the stores in flight spread over all links instead of marching in step
+                    for (uint32_t i = 0, pi = blockIdx.x % max(p.num_peers, 1u); i < p.num_peers; ++i) {
+                        ptx::tma_store_2d(&peers.m[pi], smem + L.off_d + buf * L.d_stage_bytes, c0,
                                           static_cast<int32_t>(m0));
+                        if (++pi == p.num_peers) pi = 0;
+                    }
                 }
                 ptx::tma_store_commit();
             }
@@ -592,7 +627,56 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                 if constexpr (kCta == 2) ptx::mbar_arrive_remote(&tmem_empty_bar[as], leader_rank);
                 else ptx::mbar_arrive(&tmem_empty_bar[as]);
             };
-            if (kMode == kModeSplitK || !kSk || w.kb1 - w.kb0 == p.k_blocks) {
+            if constexpr (kKs) {
+                // ---- two pairs, one tile: exchange accumulator halves through DSMEM, then store the own half
+                const uint32_t half_cols = p.block_n / 2;
+                const uint32_t half_chunks = half_cols / kEpiCols;
+                const uint32_t xchg_bytes = kBlockM * half_cols * 4;
+                const uint32_t twin = (1u - pair) * 2u + cta_rank;
+                // staging (to send) and landing (received) areas in the drained ring, [chunk][4-column group][row] of
+                // 16-byte words: a warp's 32 rows are contiguous (no bank conflicts either side)
+                uint4* send = reinterpret_cast<uint4*>(smem + L.off_a) + epi_tid;
+                const uint4* recv = reinterpret_cast<const uint4*>(smem + L.off_a + xchg_bytes) + epi_tid;
+                if (epi_tid == 0) {
+                    // this pair's MMAs are done (tmem_full), so this CTA's ring is free: arm the landing barrier and
+                    // tell the twin it may write
+                    ptx::mbar_arrive_expect_tx(xchg_recv_bar, xchg_bytes);
+                    ptx::mbar_arrive_remote(xchg_ready_bar, twin);
+                }
+                for (uint32_t c = 0; c < half_chunks; ++c) {
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32(taddr + (1u - pair) * half_cols + c * kEpiCols, v);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (uint32_t j = 0; j < 8; ++j)
+                        send[(c * 8 + j) * kBlockM] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                }
+                ptx::fence_async_smem();
+                ptx::named_bar_sync(1, 128);
+                if (epi_tid == 0) {
+                    ptx::mbar_wait(xchg_ready_bar, 0);
+                    ptx::dsmem_bulk_copy(smem_base + L.off_a + xchg_bytes, smem_base + L.off_a, xchg_bytes, xchg_recv_bar, twin);
+                }
+                ptx::mbar_wait(xchg_recv_bar, 0);
+                const uint32_t own0 = pair * half_cols;          // first column of the own half inside the tile
+                const uint32_t own_left = n0 + own0 < p.n ? p.n - (n0 + own0) : 0u;
+                const uint32_t own_chunks = (min(half_cols, own_left) + kEpiCols - 1) / kEpiCols;
+                for (uint32_t c = 0; c < own_chunks; ++c) {
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32(taddr + own0 + c * kEpiCols, v);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (uint32_t j = 0; j < 8; ++j) {
+                        const uint4 r = recv[(c * 8 + j) * kBlockM];
+                        v[4 * j + 0] = __float_as_uint(__uint_as_float(v[4 * j + 0]) + __uint_as_float(r.x));
+                        v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + __uint_as_float(r.y));
+                        v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + __uint_as_float(r.z));
+                        v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + __uint_as_float(r.w));
+                    }
+                    store_chunk(v, m0, n0 + own0 + c * kEpiCols, c, c + 1 == own_chunks);
+                }
+                release_tmem();
+            } else if (kMode == kModeSplitK || !kSk || w.kb1 - w.kb0 == p.k_blocks) {
                 for (uint32_t c = 0; c < chunks; ++c) {
                     uint32_t v[32];
                     ptx::tmem_ld_32x32(taddr + chunk_col(c), v);
@@ -716,13 +800,14 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
     }
 }
 
-template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain, bool kSk = false, bool kMc = false>
+template <int kCta, typename OutT, bool kBMn, bool kMx = false, int kMode = kModePlain, bool kSk = false, bool kMc = false,
+          bool kKs = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                   const __grid_constant__ CUtensorMap tm_d, const __grid_constant__ CUtensorMap tm_sfa,
                   const __grid_constant__ CUtensorMap tm_sfb, const __grid_constant__ PeerMaps peers,
                   const GemmParams p) {
-    gemm_sm100_body<kCta, OutT, kBMn, kMx, kMode, kSk, kMc>(tm_a, tm_b, tm_d, tm_sfa, tm_sfb, peers, p);
+    gemm_sm100_body<kCta, OutT, kBMn, kMx, kMode, kSk, kMc, kKs>(tm_a, tm_b, tm_d, tm_sfa, tm_sfb, peers, p);
 }
 
 }  // namespace dga

@@ -302,7 +302,19 @@ int finalize_plan(DgaTilingPlan& p) {
         p.blockDim = std::min(tiles, hw.smCount / cta) * cta;
         p.smemBytes = common_smem_bytes(p.n1, cta, p.stages, epi_b, in_b);
         p.workspaceBytes = 0;
-        if (p.clusterShape == 4) {
+        if (p.kernelSerial == DGA_KERNEL_CLUSTER_SPLITK) {
+            // two CTA pairs per cluster on ONE tile, each one half of K; halves exchanged through DSMEM (gemm_sm100.cuh, kKs)
+            const uint32_t kb = ceil_div(p.k, 128 / in_b);
+            const uint32_t ring = uint32_t(p.stages) * (128 * 128 + (p.n1 / cta) * 128);
+            if (cta != 2 || in_b != 2 || (p.n1 != 128 && p.n1 != 256) || tiles > clusters_of_four() || kb < 2 ||
+                ring < 2u * 128 * (p.n1 / 2) * 4) {
+                set_error("the cluster split-K variant needs ctaGroup 2, n1 of 128 or 256, at most 33 tiles and K >= 128");
+                return ACLNN_ERR_INNER_TILING_ERROR;
+            }
+            p.blockDim = tiles * 4;
+            p.clusterShape = 4;
+            p.splitkFactor = 2;
+        } else if (p.clusterShape == 4 && p.kernelSerial != DGA_KERNEL_CLUSTER_SPLITK) {
             // two CTA pairs per cluster on neighbouring N tiles, A multicast between them (gemm_sm100.cuh, kMc)
             const bool whole = p.kernelSerial == DGA_KERNEL_COMMON || p.kernelSerial == DGA_KERNEL_SMALL ||
                                p.kernelSerial == DGA_KERNEL_PADDING_COMMON;
@@ -335,6 +347,8 @@ int finalize_plan(DgaTilingPlan& p) {
                 p.blockDim = uint32_t(std::min<uint64_t>(uint64_t(dp) + uint64_t(sk) * split, clusters)) * cta;
                 p.workspaceBytes = streamk_partial_bytes(sk, split, cta, p.n1) + ((uint64_t(sk) * split * cta * 4 + 255) & ~255ull);
             }
+        } else if (p.kernelSerial == DGA_KERNEL_CLUSTER_SPLITK) {
+            // grid, cluster shape and split were set above
         } else if (p.kernelSerial != DGA_KERNEL_SMALL && p.kernelSerial != DGA_KERNEL_COMMON) {
             set_error("kernel variant " + std::to_string(int(p.kernelSerial)) + " is not built");
             return ACLNN_ERR_INNER_TILING_ERROR;
@@ -461,9 +475,29 @@ int select_kernel(DgaTilingPlan& p) {
     // weight is streamed by K slices of 128 x 128 single-CTA tiles + the reduce kernel instead, as many slices as
     // keep the grid within the SM count (audit, profiles/r01c_selector_audit.log: 16 x 4096 x 7168: 15.6 vs 31.6 us
     // plain; 16 x 2112 x 7168: 11.4 vs 31.2; 128 x 7168 x 16384: 49.6 vs 69.2).
+    // Cluster split-K (kernelSerial 6): two CTA pairs per tile, one half of K each, fp32 halves exchanged through DSMEM.
+    // Where 256-row tiles of width 128 or 256 fill 24..33 clusters of four (most of the machine) and K is long: the wide
+    // tile keeps the bytes per flop one SM can ingest, the K split fills the SMs, and the fix-up never leaves the chip.
+    // Measured (CUDA graph of 20, profiles/r02_cluster_splitk_ab.log): 512 x 4096 x 7168 26.0 vs 28.5 us plain; 256 x 4096 x
+    // 7168 18.7 vs 23.3 stream-K; 512 x 2048 x 7168 18.3 vs 22.8; 1024 x 2048 x 7168 25.3 vs 27.7; 768 x 2048 x 7168 24.3 vs 26.8;
+    // 256 x 7168 x 7168 26.2 vs 27.8.  Not for K <= 4096 (512 x 4096 x 4096 17.9 = 17.9; K = 2048: 13.2 vs 11.6) and not with
+    // fewer tiles (256 x 2048 x 7168, 16 tiles: 17.0 vs 16.6 for split-K + reduce).
+    uint32_t ks_n1 = 0;
+    if (p.m > 128 && p.layoutTagB == 1 && in_b == 2 && kb_all >= 96) {
+        for (uint32_t n1 : {128u, 256u}) {
+            const uint32_t t = ceil_div(p.m, 256) * ceil_div(p.n, n1);
+            if (t >= 24 && t <= clusters_of_four()) { ks_n1 = n1; break; }
+        }
+    }
     const uint32_t sms = platform().smCount;
     const bool rowmajor_small = p.layoutTagB == 0 && p.m <= 128 && in_b == 2 && kb_all >= 56 && 2 * tiles128 <= sms;
-    if (rowmajor_small) {
+    if (ks_n1 != 0) {
+        p.kernelSerial = DGA_KERNEL_CLUSTER_SPLITK;
+        p.ctaGroup = 2;
+        p.n1 = static_cast<uint16_t>(ks_n1);
+        p.stages = 0;
+        p.estTimeUs = best.us;
+    } else if (rowmajor_small) {
         p.kernelSerial = DGA_KERNEL_SPLITK_REDUCE;
         p.ctaGroup = 1;
         p.n1 = 128;

@@ -26,6 +26,7 @@ OPERATOR_TYPES = {
     3: "PaddingMultiCoreSplitkMatmul",
     4: "PaddingStreamkMatmul",
     5: "PaddingMultiCoreSplitkReduceMatmul",
+    6: "ClusterSplitkMatmul",
 }
 DISPATCH_POLICY_TAGS = {1: "DynamicSmall", 4: "DynamicStreamk"}   # everything else: "DynamicCommon"
 
@@ -44,7 +45,8 @@ def _describe(plan, m, n, k, layout_tag_a, layout_tag_b):
         "blockDim": plan["blockDim"],
         "kernelSerial": serial,
         "dispatchPolicyTag": DISPATCH_POLICY_TAGS.get(serial, "DynamicCommon"),
-        "ctaGroup": plan["ctaGroup"], "stages": plan["stages"], "smemBytes": plan["smemBytes"],
+        "ctaGroup": plan["ctaGroup"], "clusterShape": plan["clusterShape"], "stages": plan["stages"],
+        "smemBytes": plan["smemBytes"],
         "workspaceBytes": plan["workspaceBytes"], "estTimeUs": plan["estTimeUs"],
     }
 

@@ -188,11 +188,17 @@ def test_selector_decision_structure(dga):
     assert p["workspaceBytes"] == 8 * 256 * 2048 * 4 and p["blockDim"] == 128
     # one 256-row block whose 128-wide tiles, cut in two K slices, fill the pairs in one round -> stream-K (the
     # reference's PaddingStreamk pick at its own ragged-wave shapes, select_kernel.cpp:290-301)
-    for m in (192, 256):
-        p = dga.select_kernel(m, 4096, 7168)
+    for m, k in ((192, 4096), (256, 2048)):
+        p = dga.select_kernel(m, 4096, k)
         assert p["kernelSerial"] == 4 and p["ctaGroup"] == 2 and p["n1"] == 128 and p["splitkFactor"] == 2
         assert p["blockDim"] == 128 and p["workspaceBytes"] >= 64 * 2 * 128 * 128 * 4
-    assert dga.select_kernel(512, 4096, 7168)["kernelSerial"] in (0, 1)      # enough tiles: single pass
+    # the same block with K >= 6144: cluster split-K on 256 x 128 tiles (32 clusters of four), no workspace
+    p = dga.select_kernel(256, 4096, 7168)
+    assert p["kernelSerial"] == 6 and p["n1"] == 128 and p["blockDim"] == 128 and p["workspaceBytes"] == 0
+    # long K, 256 x 256 tiles fill 32 of the 33 clusters of four: two CTA pairs per tile, halves exchanged through DSMEM
+    ks = dga.select_kernel(512, 4096, 7168)
+    assert ks["kernelSerial"] == 6 and ks["clusterShape"] == 4 and ks["blockDim"] == 128 and ks["workspaceBytes"] == 0
+    assert dga.select_kernel(512, 4096, 4096)["kernelSerial"] in (0, 1)      # shorter K, enough tiles: single pass
     assert dga.select_kernel(256, 4096, 512)["kernelSerial"] in (0, 1)       # short K: nothing to split
     # at most one tile per cluster -> Small (select_kernel.cpp:285-289)
     assert dga.select_kernel(128, 128, 128)["kernelSerial"] in (1, 3)

@@ -122,6 +122,13 @@ ACLNN_CASES = [
     (300, 900, 1992, torch.float16, 1, {"kernelSerial": 0, "ctaGroup": 2, "n1": 240, "clusterShape": 4}),     # odd-16 width
     (640, 1024, 1024, torch.float16, 0, {"kernelSerial": 0, "ctaGroup": 2, "n1": 128, "clusterShape": 4}),    # row-major mat2
     (127, 509, 1027, torch.bfloat16, 1, {"kernelSerial": 2, "ctaGroup": 2, "n1": 64, "clusterShape": 4}),     # + repack of A, B, C
+    # cluster split-K (kernelSerial 6): two CTA pairs on one tile, one half of K each, fp32 halves exchanged through DSMEM
+    (512, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 6, "ctaGroup": 2, "n1": 256}),
+    (256, 2048, 2048, torch.bfloat16, 1, {"kernelSerial": 6, "ctaGroup": 2, "n1": 128}),
+    (300, 1000, 1992, torch.float16, 1, {"kernelSerial": 6, "ctaGroup": 2, "n1": 256}),     # ragged M, N and K
+    (256, 512, 192, torch.bfloat16, 1, {"kernelSerial": 6, "ctaGroup": 2, "n1": 256}),      # 3 K blocks: halves of 1 and 2
+    (512, 1024, 1024, torch.float16, 0, {"kernelSerial": 6, "ctaGroup": 2, "n1": 128}),     # row-major mat2
+    (127, 509, 1027, torch.bfloat16, 1, {"kernelSerial": 6, "ctaGroup": 2, "n1": 128}),     # + repack of A, B, C
 ]
 
 
