@@ -266,14 +266,18 @@ def config5_single_gpu(dga, dev, steps, warmup):
             "plan": {key: plan.get(key) for key in ("kernelSerial", "ctaGroup", "clusterShape", "n1", "stages", "blockDim")}}
 
 
-def _copy_rates(dev, nbytes):
-    """One large pinned H2D and D2H copy on their own (GB/s): what a single stream gets from this host."""
+def _copy_rates(dev, nbytes, dist):
+    """One large pinned H2D and D2H copy on their own (GB/s per rank). With several ranks a barrier right before each
+    timed copy makes them run at the same moment: the figure is what the host gives every GPU when all ask at once."""
     host = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
     devb = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     out = {}
     for name, (dst, src) in (("h2d", (devb, host)), ("d2h", (host, devb))):
         dst.copy_(src, non_blocking=True)
         torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(3):
@@ -288,15 +292,13 @@ def _e2e_rates(e2e, ms_per_step, world, dev, dist):
     """Achieved host<->device rates inside the e2e pipeline (per rank and over all ranks) and, beside them, what one
     big copy alone reaches while every rank copies at once: names the limiter of the end-to-end figure by a number."""
     h2d, d2h = e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"]
-    alone = _copy_rates(dev, 256 << 20)
-    if dist is not None:
-        dist.barrier()
+    alone = _copy_rates(dev, 256 << 20, dist)
     e2e["h2d_GBs_per_rank"] = h2d / (ms_per_step * 1e-3) / 1e9
     e2e["d2h_GBs_per_rank"] = d2h / (ms_per_step * 1e-3) / 1e9
     e2e["h2d_GBs_all_ranks"] = e2e["h2d_GBs_per_rank"] * world
     e2e["d2h_GBs_all_ranks"] = e2e["d2h_GBs_per_rank"] * world
     e2e["copy_alone_GBs"] = {"h2d": alone["h2d"], "d2h": alone["d2h"],
-                             "note": "256 MB pinned copies, every rank at the same time, nothing else running"}
+                             "note": "256 MB pinned copies, one direction at a time, every rank at the same moment (barrier), nothing else running"}
     return e2e
 
 

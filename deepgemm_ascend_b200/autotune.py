@@ -26,7 +26,7 @@ import os
 from . import _lib
 from ._lib import lib, check
 
-KERNEL_COMMON, KERNEL_SPLITK, KERNEL_STREAMK, KERNEL_SPLITK_REDUCE = 0, 3, 4, 5
+KERNEL_COMMON, KERNEL_SPLITK, KERNEL_STREAMK, KERNEL_SPLITK_REDUCE, KERNEL_CLUSTER_SPLITK = 0, 3, 4, 5, 6
 ERROR_TOLERANCE = 1e-2   # max relative error of a candidate against the fp32 golden on sampled rows
 
 
@@ -74,6 +74,18 @@ def candidate_plans(m, n, k, layout_b=1):
                 if n1 > -(-n // 16) * 16:
                     continue
                 out.append({"kernelSerial": KERNEL_COMMON, "ctaGroup": cta, "n1": n1, "stages": 0})
+    if m > 128:
+        # round 2, again appended behind everything older: clusters of four CTAs.  (1) two pairs on neighbouring N
+        # tiles with their A rows multicast (clusterShape 4): +-3 % against the pair kernel depending on how the waves
+        # fall on 66 instead of 74 pairs (profiles/r02_cluster_shapes_ab_interleaved.log) - a tuned-table pick, not an
+        # analytic one; (2) cluster split-K (two pairs on one tile, halves exchanged through DSMEM) outside the
+        # selector's window of 24-33 tiles and K >= 6144.
+        for n1 in (256, 224, 192, 128):
+            if -(-n // n1) % 2 == 0 and (layout_b == 1 or n1 % 128 == 0):
+                out.append({"kernelSerial": KERNEL_COMMON, "ctaGroup": 2, "n1": n1, "stages": 0, "clusterShape": 4})
+        for n1 in (256, 128):
+            if -(-m // 256) * -(-n // n1) <= 33 and -(-k // 64) >= 2:
+                out.append({"kernelSerial": KERNEL_CLUSTER_SPLITK, "ctaGroup": 2, "n1": n1, "stages": 0})
     return out
 
 
