@@ -519,21 +519,23 @@ static int launch_splitk_inst(const DenseLaunch& L, const SmallMParams& sp, cuda
     auto kernel = gemm_smallm_sm100_kernel<OutT>;
     int rc = set_smem_attr(kernel, L.plan.smemBytes);
     if (rc != ACLNN_SUCCESS) return rc;
-    if (sp.split > 8) DGA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    const bool ws_mode = sp.partials != nullptr;   // no cluster: the K slices meet in the workspace
+    if (sp.split > 8 && !ws_mode) DGA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(L.plan.blockDim);
     cfg.blockDim = dim3(kNumThreads);
     cfg.dynamicSmemBytes = L.plan.smemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
-    fill_launch_attrs(cfg, attr, sp.split);
+    fill_launch_attrs(cfg, attr, ws_mode ? 1u : sp.split);
     DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, sp));
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return ACLNN_SUCCESS;
 }
 
-static int launch_splitk(DenseLaunch& L, cudaStream_t stream) {
+static int launch_splitk(DenseLaunch& L, cudaStream_t stream, void* workspace = nullptr) {
     const DgaTilingPlan& p = L.plan;
+    const bool ws_mode = p.kernelSerial == DGA_KERNEL_DECODE_WS;
     const uint32_t m_pad = p.m1;
     if (!L.maps_fresh()) {
         // tm_a slot holds the weight map (UMMA A operand), tm_b the activation map (UMMA B operand)
@@ -562,6 +564,25 @@ static int launch_splitk(DenseLaunch& L, cudaStream_t stream) {
     sp.out = L.eff.d;
     static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
     sp.trace = (dbg & 16) && L.plan.blockDim * 12 <= kTraceWords ? trace_buffer() : nullptr;
+    if (ws_mode) {
+        // [split][m][pitch] fp32 slabs, the layout splitk_reduce_kernel adds up (the same reduce kernel as variant 5)
+        if (sp.k_blocks < sp.split) {
+            set_error("decode plan infeasible for this shape");
+            return ACLNN_ERR_INNER_TILING_ERROR;
+        }
+        sp.partials = static_cast<float*>(workspace);
+        sp.ws_pitch = splitk_ws_pitch(p.n);
+        L.split_ws = L.split_ws_enc = workspace;   // (no tensor map depends on it here)
+        int rcw = launch_splitk_inst<float>(L, sp, stream);   // the output type only matters to the reduce kernel
+        if (rcw != ACLNN_SUCCESS) return rcw;
+        switch (p.outDtype) {
+            case ACL_BF16: return launch_splitk_reduce<__nv_bfloat16>(L, stream);
+            case ACL_FLOAT16: return launch_splitk_reduce<__half>(L, stream);
+            case ACL_FLOAT: return launch_splitk_reduce<float>(L, stream);
+        }
+        set_error("unsupported output dtype");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
     // the drained ring doubles as the fp32 staging tile [m][128] of the reduction
     if (sp.k_blocks < sp.split || uint64_t(p.stages) * (16384 + m_pad * 128) < uint64_t(m_pad) * 512) {
         set_error("split-K plan infeasible for this shape");
@@ -582,6 +603,12 @@ static int launch_variant(DenseLaunch& L, cudaStream_t stream, void* workspace) 
         case DGA_KERNEL_SMALL:
         case DGA_KERNEL_CLUSTER_SPLITK:
         case DGA_KERNEL_PADDING_COMMON: return launch_common(L, stream, nullptr);
+        case DGA_KERNEL_DECODE_WS:
+            if (workspace == nullptr || (reinterpret_cast<uintptr_t>(workspace) & 15) != 0) {
+                set_error("the decode variant needs its (16-byte aligned) workspace");
+                return ACLNN_ERR_PARAM_INVALID;
+            }
+            return launch_splitk(L, stream, workspace);
         case DGA_KERNEL_STREAMK:
         case DGA_KERNEL_SPLITK_REDUCE:
             if (workspace == nullptr) {

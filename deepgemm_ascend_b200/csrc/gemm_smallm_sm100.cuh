@@ -34,6 +34,12 @@ struct SmallMParams {
     unsigned long long* trace; // debug: per CTA 12 words (see tools/trace_smallm.py); nullptr = off
     uint32_t prefetch_kb; // K blocks of this CTA's weight slice pulled into L2 before the grid-dependency wait
     void* out;
+    // Workspace mode (DGA_KERNEL_DECODE_WS): no cluster.  CTA (tile, slice) = (blockIdx / split, blockIdx % split) leaves
+    // its fp32 partial in slab [slice] of a [split][m][ws_pitch] workspace (coalesced: lanes = consecutive weight rows)
+    // and EXITS; splitk_reduce_kernel adds the slabs.  Nothing of the launch stays on an SM through a reduction
+    // tail, so the CTAs of the next launch on the stream move in as ours retire and start on their weights at once.
+    float* partials;
+    uint32_t ws_pitch;    // floats per workspace row (>= n)
 };
 
 struct SmallMSmem {
@@ -76,15 +82,16 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t split = p.split;
-    const uint32_t rank = split > 1 ? ptx::cluster_ctarank() : 0u;
+    const bool ws_mode = p.partials != nullptr;
     const uint32_t tile = blockIdx.x / split;
+    const uint32_t rank = ws_mode ? blockIdx.x - tile * split : (split > 1 ? ptx::cluster_ctarank() : 0u);
     const uint32_t n0 = tile * 128;
     const uint32_t stages = p.num_stages;
     // this CTA's K blocks: [kb0, kb1)
     const uint32_t kb0 = static_cast<uint32_t>((static_cast<uint64_t>(rank) * p.k_blocks) / split);
     const uint32_t kb1 = static_cast<uint32_t>((static_cast<uint64_t>(rank + 1) * p.k_blocks) / split);
 
-    const SmallMSmem L = make_smallm_smem(p.m_pad, stages, split);
+    const SmallMSmem L = make_smallm_smem(p.m_pad, stages, ws_mode ? 1u : split);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.off_bar);
     uint64_t* empty_bar = full_bar + stages;
     uint64_t* tmem_full_bar = empty_bar + stages;
@@ -98,9 +105,11 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
         // Back-to-back launches (decode: one GEMM after another): this grid becomes resident while its
         // predecessor is still draining, and HBM would sit idle through that tail and through our own first
         // round trip.  Pull the head of our weight slice into L2 now; the real loads below hit it there.
-        const uint32_t pf = min(p.prefetch_kb, kb1 - kb0);
+        // (workspace mode loads the head of the slice into the ring itself, below, and prefetches what follows it)
+        const uint32_t skip = ws_mode ? min(stages, kb1 - kb0) : 0u;
+        const uint32_t pf = min(p.prefetch_kb, kb1 - kb0 - skip);
         for (uint32_t i = 0; i < pf; ++i)
-            ptx::tma_prefetch_2d(&tm_w, static_cast<int32_t>((kb0 + i) * 64), static_cast<int32_t>(n0));
+            ptx::tma_prefetch_2d(&tm_w, static_cast<int32_t>((kb0 + skip + i) * 64), static_cast<int32_t>(n0));
     }
     if (warp == 1 && lane == 0) {
         for (uint32_t s = 0; s < stages; ++s) {
@@ -121,8 +130,18 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     // Peers will write into this CTA's reduction slots and signal its mbarrier: they may only do so once it is known
     // to be running with the barrier initialised (fence_mbar_init above).  Arrive now, wait (phase 1 of the cluster
     // barrier) just before the first remote access, a whole K slice later.
-    if (split > 1) ptx::cluster_arrive_relaxed();
+    if (split > 1 && !ws_mode) ptx::cluster_arrive_relaxed();
     if (tr != nullptr && threadIdx.x == 0) tr[3] = clock64();
+    // Workspace mode: the weights never depend on the preceding grid, so the first ring-full of weight boxes is
+    // requested BEFORE the dependency wait (real loads into shared memory, not an L2 hint); only the activations,
+    // which the predecessor may have produced, and our own stores come after it.  The bytes may complete on the
+    // full barriers before their expect_tx is posted (transiently negative transaction count).
+    const uint32_t preloaded = ws_mode ? min(stages, kb1 - kb0) : 0u;
+    if (warp == 0 && lane == 0) {
+        for (uint32_t i = 0; i < preloaded; ++i)
+            ptx::tma_load_2d(&tm_w, &full_bar[i], smem + i * L.stage_bytes, static_cast<int32_t>((kb0 + i) * 64),
+                             static_cast<int32_t>(n0), ptx::kEvictFirst);
+    }
     ptx::grid_dep_wait();   // the predecessor on the stream may still have been running up to here
     if (tr != nullptr && threadIdx.x == 0) { tr[4] = clock64(); tr[11] = ptx::globaltimer(); }
 
@@ -142,8 +161,9 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
                 for (uint32_t j = 0; j < nb; ++j, ++kb) {
                     uint8_t* sw = smem + stage * L.stage_bytes;
                     // W is read exactly once: do not let it push X out of L2
-                    ptx::tma_load_2d(&tm_w, &full_bar[stage], sw, static_cast<int32_t>(kb * 64),
-                                     static_cast<int32_t>(n0), ptx::kEvictFirst);
+                    if (kb - kb0 >= preloaded)
+                        ptx::tma_load_2d(&tm_w, &full_bar[stage], sw, static_cast<int32_t>(kb * 64),
+                                         static_cast<int32_t>(n0), ptx::kEvictFirst);
                     ptx::tma_load_2d(&tm_x, &full_bar[stage], sw + L.w_bytes, static_cast<int32_t>(kb * 64), 0,
                                      ptx::kEvictLast);
                     ptx::mbar_arrive_expect_tx(&full_bar[stage], L.stage_bytes);
@@ -180,7 +200,7 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     const uint32_t rows_per = (p.m + split - 1) / split;
     auto rows_of = [&](uint32_t d) { return d * rows_per >= p.m ? 0u : min(rows_per, p.m - d * rows_per); };
     const uint32_t my_rows = rows_of(rank);
-    if (split > 1) {
+    if (split > 1 && !ws_mode) {
         ptx::cluster_wait();   // every CTA of the cluster is running (see cluster_arrive_relaxed above)
         if (threadIdx.x == 0 && my_rows != 0) ptx::mbar_arrive_expect_tx(red_full_bar, split * my_rows * 512);
     }
@@ -207,7 +227,12 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
                 if (left > 32) ptx::tmem_ld_32x32(taddr + c + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
             }
             ptx::tmem_ld_wait();
-            if (split == 1) {
+            if (ws_mode) {
+                float* slab = p.partials + (static_cast<uint64_t>(rank) * p.m + c) * p.ws_pitch + n0 + row;
+#pragma unroll
+                for (uint32_t j = 0; j < 64; ++j)
+                    if (n_ok && j < left) __stcg(slab + static_cast<uint64_t>(j) * p.ws_pitch, __uint_as_float(v[j]));
+            } else if (split == 1) {
 #pragma unroll
                 for (uint32_t j = 0; j < 64; ++j)
                     if (n_ok && j < left)
@@ -219,7 +244,7 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
             }
         }
         ptx::tc_fence_before();
-        if (split > 1) {
+        if (split > 1 && !ws_mode) {
             ptx::fence_async_smem();          // generic-proxy writes -> visible to the bulk-copy engine
             ptx::named_bar_sync(1, 128);
             if (row < split) {
@@ -232,7 +257,7 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
         }
     }
 
-    if (split > 1) {
+    if (split > 1 && !ws_mode) {
         if (my_rows != 0) {
             ptx::mbar_wait(red_full_bar, 0);
             if (tr != nullptr && threadIdx.x == 0) tr[8] = clock64();

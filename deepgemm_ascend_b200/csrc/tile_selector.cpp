@@ -250,7 +250,37 @@ int finalize_plan(DgaTilingPlan& p) {
     const uint32_t in_b = elem_bytes(p.dtype), out_b = elem_bytes(p.outDtype);
     // PaddingCommon is Common behind a repack: the tags say what is repacked, the tile fields mean the same
     if (p.kernelSerial == DGA_KERNEL_PADDING_COMMON) p.kernelSerial = DGA_KERNEL_COMMON;
-    if (p.kernelSerial == DGA_KERNEL_SPLITK) {
+    if (p.kernelSerial == DGA_KERNEL_DECODE_WS) {
+        const uint32_t m_pad = round_up(p.m, 16);
+        const uint32_t kb = ceil_div(p.k, 64);
+        if (m_pad > 256 || p.layoutTagB != 1 || in_b != 2) {
+            set_error("the decode kernel needs m <= 256, 16-bit inputs and a [N,K] weight");
+            return ACLNN_ERR_INNER_TILING_ERROR;
+        }
+        if (p.splitkFactor == 0) p.splitkFactor = 1;
+        if (p.splitkFactor > 16 || p.splitkFactor > kb) {
+            set_error("decode split must be <= min(16, K blocks)");
+            return ACLNN_ERR_INNER_TILING_ERROR;
+        }
+        const uint32_t stage = 128 * 128 + m_pad * 128;
+        // two CTAs per SM whenever a ring of >= 3 stages fits half of the shared memory (no reduction slots here)
+        uint32_t cap = max_stages(stage, 1280, hw.smemBytes / 2 - 1024, 6);
+        if (cap < 3) cap = max_stages(stage, 1280, hw.smemBytes, 12);
+        if (p.stages == 0 || p.stages > cap) p.stages = static_cast<uint8_t>(cap);
+        if (p.stages < 2) {
+            set_error("decode plan does not fit shared memory");
+            return ACLNN_ERR_INNER_TILING_ERROR;
+        }
+        p.m1 = static_cast<uint16_t>(m_pad);
+        p.n1 = 128;
+        p.k1 = 64;
+        p.ctaGroup = 1;
+        p.clusterShape = 1;
+        p.blockDim = ceil_div(p.n, 128) * p.splitkFactor;
+        p.smemBytes = splitk_smem_bytes(m_pad, p.stages, 1);
+        p.workspaceBytes = splitk_ws_bytes(p.m, p.n, p.splitkFactor);
+        p.paddingTagC = 0;   // the reduce kernel stores C with plain st.global: any pitch will do
+    } else if (p.kernelSerial == DGA_KERNEL_SPLITK) {
         const uint32_t m_pad = round_up(p.m, 16);
         if (m_pad > 256 || p.layoutTagB != 1 || in_b != 2) {
             set_error("split-K small-M kernel needs m <= 256, 16-bit inputs and a [N,K] weight");

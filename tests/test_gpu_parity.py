@@ -129,6 +129,16 @@ ACLNN_CASES = [
     (256, 512, 192, torch.bfloat16, 1, {"kernelSerial": 6, "ctaGroup": 2, "n1": 256}),      # 3 K blocks: halves of 1 and 2
     (512, 1024, 1024, torch.float16, 0, {"kernelSerial": 6, "ctaGroup": 2, "n1": 128}),     # row-major mat2
     (127, 509, 1027, torch.bfloat16, 1, {"kernelSerial": 6, "ctaGroup": 2, "n1": 128}),     # + repack of A, B, C
+    # decode through the workspace (kernelSerial 7): no cluster, fp32 K-slice slabs + the reduce kernel
+    (64, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 7, "splitkFactor": 8}),
+    (128, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 7, "splitkFactor": 9}),           # slices of 12 and 13 K blocks
+    (1, 4096, 7168, torch.bfloat16, 1, {"kernelSerial": 7, "splitkFactor": 8}),
+    (16, 256, 512, torch.bfloat16, 1, {"kernelSerial": 7, "splitkFactor": 2}),
+    (50, 1000, 1992, torch.bfloat16, 1, {"kernelSerial": 7, "splitkFactor": 3}),            # ragged N and K, rows not a multiple of 16
+    (7, 520, 1992, torch.float16, 1, {"kernelSerial": 7, "splitkFactor": 7}),
+    (100, 1000, 1000, torch.bfloat16, 1, {"kernelSerial": 7, "splitkFactor": 1}),
+    (200, 2048, 4096, torch.bfloat16, 1, {"kernelSerial": 7, "splitkFactor": 4}),
+    (33, 509, 1027, torch.bfloat16, 1, {"kernelSerial": 7, "splitkFactor": 4}),             # + repack of A and B
 ]
 
 
