@@ -234,7 +234,10 @@ def test_tile_widths_that_are_odd_multiples_of_16(dga):
     import deepgemm_ascend_b200.autotune as at
     cands = at.candidate_plans(2048, 4096, 7168)
     odd = [i for i, p in enumerate(cands) if p.get("n1", 0) % 32 == 16]
-    assert odd and odd[0] > max(i for i, p in enumerate(cands) if p.get("n1", 0) % 32 == 0 or "n1" not in p)
+    round2 = [i for i, p in enumerate(cands) if p.get("clusterShape") == 4 or p["kernelSerial"] == 6]
+    older = [i for i, p in enumerate(cands) if (p.get("n1", 0) % 32 == 0 or "n1" not in p) and i not in round2]
+    assert odd and odd[0] > max(older)
+    assert round2 and round2[0] > odd[-1]          # the round-2 cluster candidates come behind those again
 
 
 def test_cluster_shape_rules(dga, tmp_path):
