@@ -709,7 +709,8 @@ struct Fp8Launch {
     const void* encoded_ws = nullptr;
 };
 
-static const uint32_t kFp8TilesPair[] = {256, 224, 192, 128};
+static const uint32_t kFp8TilesPair[] = {256, 224, 192, 160, 128};
+static std::atomic<int64_t> g_opt_fp8_bn{-1};   // tile width of the fp32-scale fp8 kernel (sweeps; -1: the cost rule)
 static const uint32_t kMxTilesPair[] = {224, 192, 128};   // 2 accumulator stages + scale columns must fit 512 TMEM columns
 
 // Wave-balanced tile for the fp8 kernel: fewest (waves x block_n) column-units, ties to the wider tile.
@@ -723,9 +724,16 @@ static void plan_fp8(Fp8Launch& L) {
         for (uint32_t bn : kFp8TilesPair) {
             const uint64_t tiles = uint64_t(ceil_div(L.m, 256)) * ceil_div(L.n, bn);
             const uint64_t waves = (tiles + hw.smCount / 2 - 1) / (hw.smCount / 2);
-            const uint64_t cost = waves * bn;
+            // measured time of one K block of a tile, ns (profiles/r02_fp8_tile_sweep.log: it is dominated by the
+            // per-K-block cost of the MMA <-> promotion hand-over, not by the tile width, so wide tiles win unless
+            // they cost a whole extra wave)
+            const uint64_t step_ns = bn == 256 ? 539 : bn == 224 ? 555 : bn == 192 ? 505 : bn == 160 ? 499 : 450;
+            const uint64_t cost = waves * step_ns;
             if (cost < best) { best = cost; L.bn = bn; }
         }
+        const int64_t forced = g_opt_fp8_bn.load(std::memory_order_relaxed);
+        for (uint32_t bn : kFp8TilesPair)
+            if (forced == int64_t(bn)) L.bn = bn;
     }
     const uint32_t per_stage = 128 * 128 + (L.bn / L.cta) * 128;
     const uint32_t kb_count = ceil_div(L.k, 128);
@@ -946,6 +954,7 @@ static int launch_fp8(Fp8Launch& L, void* workspace, cudaStream_t stream) {
         case 256: return launch_fp8_inst<2, 256>(L, fp, stream);
         case 224: return launch_fp8_inst<2, 224>(L, fp, stream);
         case 192: return launch_fp8_inst<2, 192>(L, fp, stream);
+        case 160: return launch_fp8_inst<2, 160>(L, fp, stream);
         case 128: return launch_fp8_inst<2, 128>(L, fp, stream);
     }
     set_error("fp8 tile not instantiated");
@@ -1651,6 +1660,7 @@ aclnnStatus dgaSetOption(const char* name, int64_t value) {
     else if (std::strcmp(name, "splitk_issue_batch") == 0) g_opt_splitk_batch.store(value);
     else if (std::strcmp(name, "raster_group") == 0) g_opt_raster.store(value);
     else if (std::strcmp(name, "raster_along_m") == 0) g_opt_raster_dir.store(value);
+    else if (std::strcmp(name, "fp8_bn") == 0) g_opt_fp8_bn.store(value);
     else if (std::strcmp(name, "streamk_cooperative") == 0) g_opt_sk_coop.store(value < 0 ? 1 : value);
     else if (std::strcmp(name, "hint_a") == 0) g_opt_hint_a.store(value);
     else if (std::strcmp(name, "hint_b") == 0) g_opt_hint_b.store(value);

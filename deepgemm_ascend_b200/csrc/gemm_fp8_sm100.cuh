@@ -61,8 +61,8 @@ __host__ __device__ inline Fp8Smem make_fp8_smem(uint32_t block_n, uint32_t cta,
     l.off_b = l.off_a + stages * l.a_stage_bytes;
     l.off_sfb = l.off_b + stages * l.b_stage_bytes;
     l.off_bar = l.off_sfb + 2 * 3 * l.sfb_pitch * 4;
-    // full[stages] empty[stages] part_full[2 buffers][2 halves] part_empty[2][2] + tmem ptr
-    l.total = l.off_bar + (2 * stages + 8) * 8 + 16;
+    // full[stages] empty[stages] part_full[<= 4 buffers][2 halves] part_empty[<= 4][2] + tmem ptr
+    l.total = l.off_bar + (2 * stages + 16) * 8 + 16;
     return l;
 }
 
@@ -111,8 +111,11 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
         ptx::grid_dep_wait();     // the flag was written by a previous grid
         if (*p.gate != p.gate_expect) return;   // grid-uniform
     }
-    constexpr uint32_t kTmemCols = (2 * kBN <= 32) ? 32 : (2 * kBN <= 64) ? 64 : (2 * kBN <= 128) ? 128
-                                   : (2 * kBN <= 256) ? 256 : 512;
+    // TMEM buffers of kBN columns: as many as the 512 columns hold (2 for 256..192, 3 for 160, 4 for 128).  Each is two
+    // half buffers with their own barriers; the more are in flight, the more of the MMA <-> promotion handshake
+    // (~1500 clocks from "MMAs of a half done" to "next MMAs into that half issued") hides behind other halves' MMAs.
+    constexpr uint32_t kNumBuf = (512 / kBN) > 4 ? 4 : (512 / kBN);
+    constexpr uint32_t kTmemCols = 512;
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -132,8 +135,8 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L.off_bar);
     uint64_t* empty_bar = full_bar + stages;
     uint64_t* part_full_bar = empty_bar + stages;    // [buffer * 2 + half] partial product of one K block is in TMEM
-    uint64_t* part_empty_bar = part_full_bar + 4;    // [buffer * 2 + half] that half's promotion warps have read it
-    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(part_empty_bar + 4);
+    uint64_t* part_empty_bar = part_full_bar + 8;    // [buffer * 2 + half] that half's promotion warps have read it
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(part_empty_bar + 8);
 
     if constexpr (kCta == 2) ptx::cluster_sync();
 
@@ -147,7 +150,7 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             ptx::mbar_init(&full_bar[s], kCta);
             ptx::mbar_init(&empty_bar[s], 1);
         }
-        for (uint32_t s = 0; s < 4; ++s) {
+        for (uint32_t s = 0; s < 2 * kNumBuf; ++s) {
             ptx::mbar_init(&part_full_bar[s], 1);
             ptx::mbar_init(&part_empty_bar[s], kCta * 4);   // one elected arrive per warp of the owning group, both CTAs
         }
@@ -207,7 +210,7 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             uint32_t stage = 0, phase = 0, pc = 0;   // pc: running K-block counter (selects the TMEM buffer)
             for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters) {
                 for (uint32_t kb = 0; kb < k_blocks; ++kb, ++pc) {
-                    const uint32_t buf = pc & 1, par = (pc >> 1) & 1;
+                    const uint32_t buf = pc % kNumBuf, par = (pc / kNumBuf) & 1;
                     ptx::mbar_wait(&full_bar[stage], phase);
 #pragma unroll
                     for (uint32_t h = 0; h < 2; ++h) {
@@ -282,16 +285,13 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             ptx::named_bar_sync(3, 256);
         }
 
-        // loop invariants of the promotion chain: barrier addresses (the arrival goes to the leader CTA's barrier),
-        // TMEM addresses of this group's half in both buffers
-        uint32_t pf_addr[2], pe_addr[2], taddr[2];
-#pragma unroll
-        for (uint32_t b = 0; b < 2; ++b) {
-            pf_addr[b] = ptx::smem_u32(&part_full_bar[b * 2 + group]);
-            pe_addr[b] = ptx::smem_u32(&part_empty_bar[b * 2 + group]);
-            if constexpr (kCta == 2) pe_addr[b] = ptx::mapa(pe_addr[b], 0);
-            taddr[b] = tmem_base + ((quad * 32) << 16) + b * kBN + group * kHalf;
-        }
+        // loop invariants of the promotion chain: barrier addresses (the arrival goes to the leader CTA's barrier) and the
+        // TMEM address of this group's half, per buffer by plain arithmetic (a dynamically indexed array would go to
+        // local memory)
+        const uint32_t pf_addr0 = ptx::smem_u32(&part_full_bar[group]);
+        uint32_t pe_addr0 = ptx::smem_u32(&part_empty_bar[group]);
+        if constexpr (kCta == 2) pe_addr0 = ptx::mapa(pe_addr0, 0);
+        const uint32_t taddr0 = tmem_base + ((quad * 32) << 16) + group * kHalf;
 
         for (uint32_t t = cluster_id; t < num_tiles; t += num_clusters, tile_par ^= 1) {
             uint32_t mb, nb;
@@ -315,67 +315,59 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             // One K block: fold this group's half of the partial product into the running sums.  kBuf is a literal
             // in every call below (the loop is unrolled by four), sa the row's activation scale of this block.
             auto promote = [&](uint32_t kb, uint32_t buf, uint32_t par, float sa) __attribute__((always_inline)) {
+                const uint32_t pf_addr = pf_addr0 + buf * 16, pe_addr = pe_addr0 + buf * 16, taddr = taddr0 + buf * kBN;
                 const float pa = sa * sfb_a[kb], pb = sa * sfb_b[kb];
                 float s[kUnits];
 #pragma unroll
                 for (uint32_t u = 0; u < kUnits; ++u)
                     s[u] = __uint_as_float((take_a[u] & __float_as_uint(pa)) | (~take_a[u] & __float_as_uint(pb)));
-                ptx::mbar_wait_addr(pf_addr[buf], par);
+                ptx::mbar_wait_addr(pf_addr, par);
                 ptx::tc_fence_after();
-                uint32_t va[32], vb[32];
-                ptx::tmem_ld_32x32(taddr[buf], va);
+                // tcgen05.wait::ld waits for EVERY outstanding load of the thread, so loads cannot be pipelined one behind
+                // the other: each wait exposes a full TMEM round trip (~150 clocks with MMAs running).  Hence batches of
+                // 64 columns (two loads back to back, one wait, 32 packed FMAs) instead of one 32-column load per wait:
+                // half as many round trips per K block (profiles/r02_fp8_tile_sweep.log: the time per K block was
+                // ~550 clocks + 1.5 per column whatever the tile width and however many TMEM buffers were in flight).
+                constexpr uint32_t kBatches = (kHalf + 63) / 64;
 #pragma unroll
-                for (uint32_t i = 0; i < kLoads; ++i) {
+                for (uint32_t b = 0; b < kBatches; ++b) {
+                    const uint32_t c0 = 64 * b;                       // first column of the batch inside the half
+                    uint32_t v[64];
+                    if (c0 + 32 <= kHalf) ptx::tmem_ld_32x32(taddr + c0, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+                    else ptx::tmem_ld_32x16(taddr + c0, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
+                    if (c0 + 64 <= kHalf) ptx::tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+                    else if (c0 + 48 <= kHalf) ptx::tmem_ld_32x16(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[16]>(&v[32]));
                     ptx::tmem_ld_wait();
-                    // the next load flies while this one is folded in
-                    if (i + 1 < kLoads) {
-                        uint32_t(&nxt)[32] = (i & 1) ? va : vb;
-                        if (32 * (i + 2) <= kHalf) ptx::tmem_ld_32x32(taddr[buf] + 32 * (i + 1), nxt);
-                        else ptx::tmem_ld_32x16(taddr[buf] + 32 * (i + 1), *reinterpret_cast<uint32_t(*)[16]>(&nxt[0]));
-                    } else {
+                    if (b + 1 == kBatches) {
                         // the whole half is in registers: hand its TMEM buffer back to the tensor core
                         ptx::tc_fence_before();
                         __syncwarp();
                         if (ptx::elect_one()) {
-                            if constexpr (kCta == 2) ptx::mbar_arrive_cluster_addr(pe_addr[buf]);
-                            else ptx::mbar_arrive_addr(pe_addr[buf]);
+                            if constexpr (kCta == 2) ptx::mbar_arrive_cluster_addr(pe_addr);
+                            else ptx::mbar_arrive_addr(pe_addr);
                         }
                     }
-                    const uint32_t(&cur)[32] = (i & 1) ? vb : va;
 #pragma unroll
-                    for (uint32_t j = 0; j < 32; j += 2) {
-                        if (32 * i + j < kHalf)
-                            ptx::fma2(acc[32 * i + j], acc[32 * i + j + 1], __uint_as_float(cur[j]), __uint_as_float(cur[j + 1]),
-                                      s[(32 * i + j) / 16]);
+                    for (uint32_t j = 0; j < 64; j += 2) {
+                        if (c0 + j < kHalf)
+                            ptx::fma2(acc[c0 + j], acc[c0 + j + 1], __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                      s[(c0 + j) / 16]);
                     }
                 }
             };
 
-            // this row's activation scales of K blocks [4g, 4g + 4) are in registers while group g runs; group g + 1
-            // is in flight.  pc counts K blocks over the whole kernel: buffer = pc & 1, barrier parity = (pc >> 1) & 1.
+            // this row's activation scales of K blocks [4g, 4g + 4) are in registers while group g runs; group g + 1 is
+            // in flight.  pc counts K blocks over the whole kernel: buffer = pc % kNumBuf, barrier parity = (pc / kNumBuf) & 1.
             const bool vec = (reinterpret_cast<uintptr_t>(p.sfa) & 15) == 0 && (p.sfa_ld & 3) == 0;
-            float4 sa4n = load_scales4(sfa_row, 0, k_blocks, vec);
-            uint32_t kb = 0;
-            for (; kb + 4 <= k_blocks; kb += 4, pc += 4) {
-                const float4 sa4 = sa4n;
-                if (kb + 4 < k_blocks) sa4n = load_scales4(sfa_row, kb + 4, k_blocks, vec);
-                const uint32_t b0 = pc & 1, par0 = (pc >> 1) & 1;
-                if (b0 == 0) {
-                    promote(kb, 0, par0, sa4.x);
-                    promote(kb + 1, 1, par0, sa4.y);
-                    promote(kb + 2, 0, par0 ^ 1, sa4.z);
-                    promote(kb + 3, 1, par0 ^ 1, sa4.w);
-                } else {
-                    promote(kb, 1, par0, sa4.x);
-                    promote(kb + 1, 0, par0 ^ 1, sa4.y);
-                    promote(kb + 2, 1, par0 ^ 1, sa4.z);
-                    promote(kb + 3, 0, par0, sa4.w);
+            float4 sa4 = load_scales4(sfa_row, 0, k_blocks, vec);
+            float4 sa4n = sa4;
+            for (uint32_t kb = 0; kb < k_blocks; ++kb, ++pc) {
+                const uint32_t ki = kb & 3;
+                if (ki == 0) {
+                    if (kb != 0) sa4 = sa4n;
+                    if (kb + 4 < k_blocks) sa4n = load_scales4(sfa_row, kb + 4, k_blocks, vec);
                 }
-            }
-            for (uint32_t i = 0; kb < k_blocks; ++kb, ++pc, ++i) {   // K not a multiple of 512
-                const float sa = pick4(sa4n, i);
-                if ((pc & 1) == 0) promote(kb, 0, (pc >> 1) & 1, sa);
-                else promote(kb, 1, (pc >> 1) & 1, sa);
+                promote(kb, pc % kNumBuf, (pc / kNumBuf) & 1, pick4(sa4, ki));
             }
 
             // ---- tile done: registers -> bf16 -> swizzled smem -> TMA store (per warp group, 32-column boxes; when
