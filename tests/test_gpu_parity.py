@@ -339,6 +339,30 @@ def test_side_stream_launch_keeps_its_workspace(dga):
         assert orc.max_rel_err(out.float().cpu().numpy(), ref) <= 2.0 ** -7
 
 
+def test_concurrent_stream_k_launches_do_not_wait_on_each_other(dga):
+    """Stream-K CTAs spin on flags that other CTAs of the SAME launch set, so every CTA of a launch has to be on the
+    device at once. The launch is cooperative: two stream-K launches queued on two streams, each with
+    its own workspace, run one after the other instead of interleaving half-resident grids that would wait on each
+    other until the in-kernel deadline traps. Both must finish and match the oracle."""
+    m, n, k = 256, 4096, 2048
+    assert dga.select_kernel(m, n, k)["kernelSerial"] == 4
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    jobs = []
+    for i, s in enumerate(streams):
+        a, b = _inputs(m, n, k, torch.bfloat16, seed=41 + i)
+        ta, w = _to_dev(a, torch.bfloat16), _to_dev(b.T, torch.bfloat16)
+        out = torch.zeros((m, n), dtype=torch.bfloat16, device=DEV)
+        jobs.append((dga.Executor(ta, w.t(), out), out, orc.golden_fp64(a, b), s))
+    torch.cuda.synchronize()
+    for _ in range(50):
+        for exe, _, _, s in jobs:
+            exe(s)
+    torch.cuda.synchronize()
+    for exe, out, ref, _ in jobs:
+        assert orc.max_rel_err(out.float().cpu().numpy(), ref) <= 1e-2
+        exe.close()
+
+
 def test_executor_repeatable_and_graph_capturable(dga):
     a, b = _inputs(256, 512, 256, torch.bfloat16, seed=9)
     ta, w = _to_dev(a, torch.bfloat16), _to_dev(b.T, torch.bfloat16)
