@@ -14,6 +14,7 @@ ACLNN_SUCCESS = 0
 
 KERNEL_COMMON, KERNEL_SMALL, KERNEL_PADDING_COMMON, KERNEL_SPLITK, KERNEL_STREAMK = 0, 1, 2, 3, 4
 KERNEL_SPLITK_REDUCE, KERNEL_CLUSTER_SPLITK = 5, 6
+NO_ALLOC_SCRATCH_BYTES = 32 << 20   # DGA_NO_ALLOC_SCRATCH_BYTES (include/dga_b200.h)
 KERNEL_NAMES = {0: "Common", 1: "Small", 2: "PaddingCommon", 3: "SplitK", 4: "StreamK", 5: "SplitKReduce", 6: "ClusterSplitK"}
 
 
@@ -73,6 +74,7 @@ SIGNATURES = {
     "dgaGetPlatformInfo": (_i32, [_P(PlatformInfo)]),
     "dgaSetPlatformInfo": (_i32, [_P(PlatformInfo)]),
     "dgaMatmulWithPlan": (_i32, [_P(AclTensor), _P(AclTensor), _P(AclTensor), _P(TilingPlan), _vp, _u64, _vp]),
+    "dgaSplitkMatmulNoAlloc": (_i32, [_vp, _vp, _vp, _u32, _u32, _u32, _i32, _i32, _i32, _u32, _vp]),
     "dgaRunMmadCustom": (_i32, [_vp, _vp, _vp, _vp]),
     "dgaRunMmadRtc": (_i32, [_vp, _vp, _vp, _u32, _u32, _u32, _u32, _vp]),
     "dgaRunMmadBench": (_i32, [_vp, _vp, _vp, _u32, _u32, _u32, _P(_i32), _vp]),

@@ -1743,3 +1743,126 @@ uint64_t dgaKernelLaunchCount(void) { return g_launches.load(); }
 const char* dgaVersion(void) { return "dga-b200 0.1 (sm_100a)"; }
 
 }  // extern "C"
+
+// ======================================================== matmul without any device allocation ====
+// dgaSplitkMatmulNoAlloc (include/dga_b200.h).  No counterpart in the reference; added
+// for callers that cannot allocate (graph capture, serving loops).  Nothing above this line changes.
+//
+// The fp32 partial slabs of the split-K + reduce variant, which every other entry point keeps in the caller's
+// workspace.  One array per GPU that loads this module, held until the process exits, shared by every call on that
+// GPU: overlapping calls race.  In HOST code the name below is only a stand-in for the device array - handing it to a
+// kernel or a tensor map would pass a host address - so its device address is looked up with cudaGetSymbolAddress,
+// once per device with that device current (no_alloc_scratch).
+static __device__ __align__(256) unsigned char g_no_alloc_scratch[DGA_NO_ALLOC_SCRATCH_BYTES];
+
+namespace dga {
+
+constexpr int kMaxDevices = 64;
+
+static int no_alloc_scratch(void** out) {
+    static std::mutex mu;
+    static void* addr[kMaxDevices] = {};
+    const int dev = current_device();
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("device ordinal " + std::to_string(dev) + " is beyond the table of the no-allocation entry point");
+        return ACLNN_ERR_RUNTIME_ERROR;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (addr[dev] == nullptr) {
+        void* p = nullptr;
+        DGA_CUDA(cudaGetSymbolAddress(&p, g_no_alloc_scratch));
+        if (p == nullptr || (reinterpret_cast<uintptr_t>(p) & 255) != 0) {
+            set_error("static scratch array has no usable device address");
+            return ACLNN_ERR_RUNTIME_ERROR;
+        }
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return ACLNN_SUCCESS;
+}
+
+// The split-K GEMM launch of launch_common_inst without its run-time-compilation branch (which loads modules).
+template <bool kBMn>
+static int launch_splitk_gemm_static(const DenseLaunch& L, const GemmParams& gp, cudaStream_t stream) {
+    auto kernel = gemm_sm100_kernel<2, float, kBMn, false, kModeSplitK, false, false, false>;
+    int rc = set_smem_attr(kernel, L.plan.smemBytes);
+    if (rc != ACLNN_SUCCESS) return rc;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(L.plan.blockDim);
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.dynamicSmemBytes = L.plan.smemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    fill_launch_attrs(cfg, attr, 2);
+    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, L.tm_a, L.tm_b, L.tm_d, L.tm_a, L.tm_b, L.peers, gp));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return ACLNN_SUCCESS;
+}
+
+}  // namespace dga
+
+extern "C" aclnnStatus dgaSplitkMatmulNoAlloc(const void* self, const void* mat2, void* out, uint32_t m, uint32_t n,
+                                              uint32_t k, int32_t dtype, int32_t outDtype, int32_t layoutTagB,
+                                              uint32_t splitkFactor, aclrtStream stream) {
+    if (self == nullptr || mat2 == nullptr || out == nullptr) return ACLNN_ERR_PARAM_NULLPTR;
+    if (m == 0 || n == 0 || k == 0 || (dtype != ACL_BF16 && dtype != ACL_FLOAT16) ||
+        (outDtype != dtype && outDtype != ACL_FLOAT) || (layoutTagB != 0 && layoutTagB != 1)) {
+        set_error("dgaSplitkMatmulNoAlloc: m, n, k > 0, 16-bit inputs, output of the input type or fp32, layoutTagB 0 or 1");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    const uint32_t kb = ceil_div(k, 64);
+    if (kb < 2 || (splitkFactor != 0 && (splitkFactor < 2 || splitkFactor > 16 || splitkFactor > kb))) {
+        set_error("dgaSplitkMatmulNoAlloc: splitkFactor is 0 (automatic) or 2..min(16, ceil(k / 64)), and k > 64");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    uint32_t split = splitkFactor;
+    if (split == 0) {
+        // as many K slices as fill the CTA pairs once; fewer when the slabs would not fit the static array
+        const uint32_t tiles = ceil_div(m, 256) * ceil_div(n, 256), clusters = platform().smCount / 2;
+        split = std::min(std::min(std::max(clusters / std::max(tiles, 1u), 2u), 16u), kb);
+        while (split > 2 && splitk_ws_bytes(m, n, split) > DGA_NO_ALLOC_SCRATCH_BYTES) --split;
+    }
+    const uint64_t need = splitk_ws_bytes(m, n, split);
+    if (need > DGA_NO_ALLOC_SCRATCH_BYTES) {
+        set_error("dgaSplitkMatmulNoAlloc: " + std::to_string(m) + " x " + std::to_string(n) + " with " +
+                  std::to_string(split) + " K slices needs " + std::to_string(need) +
+                  " bytes of scratch, the static array holds " + std::to_string(DGA_NO_ALLOC_SCRATCH_BYTES) +
+                  " (DGA_NO_ALLOC_SCRATCH_BYTES); use the two-phase entry with a caller workspace");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    DenseLaunch L;
+    seed_plan(L.plan, m, n, k, dtype, outDtype, layoutTagB);
+    L.plan.kernelSerial = DGA_KERNEL_SPLITK_REDUCE;
+    L.plan.ctaGroup = 2;
+    L.plan.n1 = 256;
+    L.plan.splitkFactor = uint16_t(split);
+    L.a = self; L.b = mat2; L.d = out;
+    L.lda = k; L.ldb = layoutTagB == 1 ? k : n; L.ldd = n;
+    int rc = apply_padding(L, /*allow_repack=*/false);   // finalize_plan: stages, grid, shared memory, workspaceBytes
+    if (rc != ACLNN_SUCCESS) return rc;
+    if (L.plan.kernelSerial != DGA_KERNEL_SPLITK_REDUCE || L.plan.workspaceBytes != need) {
+        set_error("dgaSplitkMatmulNoAlloc: the plan came back as another variant");
+        return ACLNN_ERR_INNER_TILING_ERROR;
+    }
+    void* scratch = nullptr;
+    rc = no_alloc_scratch(&scratch);
+    if (rc != ACLNN_SUCCESS) return rc;
+    L.mode = kModeSplitK;
+    L.split_ws = scratch;
+    L.eff = {L.a, L.b, L.d, L.lda, L.ldb, L.ldd};
+    rc = encode_common(L);   // host-only: three tensor maps, the output map over the static array
+    if (rc != ACLNN_SUCCESS) return rc;
+    GemmParams gp{};
+    common_params(L.plan, gp);
+    gp.split_k = L.plan.splitkFactor;
+    gp.dp_tiles *= L.plan.splitkFactor;
+    gp.epi_cols = 32;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    rc = layoutTagB == 1 ? launch_splitk_gemm_static<false>(L, gp, s) : launch_splitk_gemm_static<true>(L, gp, s);
+    if (rc != ACLNN_SUCCESS) return rc;
+    switch (outDtype) {
+        case ACL_BF16: return launch_splitk_reduce<__nv_bfloat16>(L, s);
+        case ACL_FLOAT16: return launch_splitk_reduce<__half>(L, s);
+        default: return launch_splitk_reduce<float>(L, s);
+    }
+}

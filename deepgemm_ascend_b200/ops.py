@@ -153,6 +153,29 @@ def matmul_with_plan(self, mat2, out, stream=None, **fields):
 _PLAN_WS = None
 
 
+def splitk_matmul_no_alloc(self, mat2, out, splitk_factor=0, stream=None):
+    """out = self @ mat2 through dgaSplitkMatmulNoAlloc: the split-K + reduce variant with its fp32 slabs in the
+    library's static device array (at most _lib.NO_ALLOC_SCRATCH_BYTES), no device allocation inside the call.
+    Contiguous operands; mat2 is a [N, K] tensor viewed as [K, N] (`w.t()`) or a contiguous [K, N] tensor. No
+    counterpart in the reference (see include/dga_b200.h). Calls that overlap on the GPU race on the array."""
+    _require_cuda(self, mat2, out)
+    m, k = self.shape
+    n = out.shape[1]
+    if mat2.shape != (k, n) or out.shape[0] != m or not (self.is_contiguous() and out.is_contiguous()):
+        raise ValueError("splitk_matmul_no_alloc: contiguous self [m,k], out [m,n]; mat2 [k,n]")
+    if mat2.is_contiguous():
+        layout_b = 0
+    elif mat2.t().is_contiguous():
+        layout_b = 1
+    else:
+        raise ValueError("splitk_matmul_no_alloc: mat2 is a contiguous [k,n] tensor or the .t() of a contiguous [n,k] one")
+    check(lib.dgaSplitkMatmulNoAlloc(ctypes.c_void_p(self.data_ptr()), ctypes.c_void_p(mat2.data_ptr()),
+                                     ctypes.c_void_p(out.data_ptr()), m, n, k, acl_dtype(self.dtype),
+                                     acl_dtype(out.dtype), layout_b, int(splitk_factor), _stream_ptr(stream)),
+          "dgaSplitkMatmulNoAlloc")
+    return out
+
+
 def set_option(name, value):
     """Process-wide tuning knob (see dgaSetOption in include/dga_b200.h); value < 0 restores the default."""
     check(lib.dgaSetOption(name.encode(), int(value)), "dgaSetOption")
