@@ -27,6 +27,7 @@ The oracle (oracle/) is used only for the cpu_baseline leg and for --impl refere
 """
 import argparse
 import json
+import re
 import os
 import sys
 import threading
@@ -78,6 +79,11 @@ def workload_shape(name, world):
         return dict(m=4096, n=7168, k=16384, dtype="fp8", n_total=7168 * world, scaling="weak")
     if name == "moe":
         return dict(m=8192, n=4096, k=7168, dtype="bf16", n_total=4096 * world, scaling="weak", groups=8)
+    if re.fullmatch(r"m\d+pair", name):    # two decode GEMMs (N = 4096 each) sharing X in one launch: dgaDecodePairMatmul
+        return dict(m=int(name[1:-4]), n=8192, k=7168, dtype="bf16", n_total=8192 * world, scaling="weak", pair=True)
+    if re.fullmatch(r"m\d+n\d+", name):   # decode-sized probes at another N (same K), e.g. m64n8192
+        mm, nn = (int(x) for x in name[1:].split("n"))
+        return dict(m=mm, n=nn, k=7168, dtype="bf16", n_total=nn * world, scaling="weak")
     if name.startswith("m") and name[1:].isdigit():
         return dict(m=int(name[1:]), n=4096, k=7168, dtype="bf16", n_total=4096 * world, scaling="weak")
     raise SystemExit("unknown workload %s" % name)

@@ -65,7 +65,14 @@ def run_ours(args, rank, world):
         a_bufs = [torch.randn((m, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
         w_bufs = [torch.randn((n, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]  # [N,K]
         c_bufs = [torch.empty((m, n), device=dev, dtype=torch.bfloat16) for _ in range(sets)]
-        if workload == "moe":
+        if shape.get("pair"):
+            # the two weights are separate allocations; C_first and C_second are the column halves of one [m, n] buffer
+            h = n // 2
+            w_second = [torch.randn((h, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
+            w_bufs = [torch.randn((h, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
+            execs = [dga.DecodePair(a_bufs[i], w_bufs[i].t(), c_bufs[i][:, :h], w_second[i].t(), c_bufs[i][:, h:])
+                     for i in range(sets)]
+        elif workload == "moe":
             g = shape["groups"]
             w_bufs = [torch.randn((g, n, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
             index = torch.arange(g, device=dev, dtype=torch.int32).repeat_interleave(m // g)
@@ -139,7 +146,7 @@ def run_ours(args, rank, world):
 
     # ---- e2e: host buffers in, host buffer out, through the public operator call
     e2e = e2e_run(dga, dev, m, n, k, steps=max(3, min(args.steps, 20)), flops=flops, world=world, dist=dist, fp8=fp8,
-                  groups=shape.get("groups", 0))
+                  groups=shape.get("groups", 0), pair=bool(shape.get("pair")))
 
     # ---- optional: all-gather of C over NVLink (only when the caller needs the full output)
     gather = None
@@ -302,7 +309,7 @@ def _e2e_rates(e2e, ms_per_step, world, dev, dist):
     return e2e
 
 
-def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False, groups=0):
+def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False, groups=0, pair=False):
     """Same metric end to end: every step copies its A and W from pinned host memory to the device, calls the
     operator and copies C back to pinned host memory, all inside the timed region.  The three legs run on three
     streams over a ring of 2 device buffer sets, so the copies of step i+1 and i-1 overlap the GEMM of step i
@@ -346,6 +353,9 @@ def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False, groups=0):
                 dga.fp8_block_scaled_matmul(da[i], dsa[i], dw[i], dsw[i], out=dc[i])
             elif groups:
                 dga.m_grouped_matmul(da[i], dw[i], index, out=dc[i])
+            elif pair:   # the two weights are the row halves of the host buffer, the two outputs the column halves
+                h = n // 2
+                dga.decode_pair_matmul(da[i], dw[i][:h].t(), dw[i][h:].t(), dc[i][:, :h], dc[i][:, h:])
             else:
                 dga.catlass_dynamic_matmul(da[i], dw[i].t(), out=dc[i])     # two-phase C ABI underneath
             mm_done[i].record(s_mm)

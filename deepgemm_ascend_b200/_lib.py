@@ -74,6 +74,7 @@ SIGNATURES = {
     "dgaGetPlatformInfo": (_i32, [_P(PlatformInfo)]),
     "dgaSetPlatformInfo": (_i32, [_P(PlatformInfo)]),
     "dgaMatmulWithPlan": (_i32, [_P(AclTensor), _P(AclTensor), _P(AclTensor), _P(TilingPlan), _vp, _u64, _vp]),
+    "dgaDecodePairMatmul": (_i32, [_P(AclTensor)] * 5 + [_vp]),
     "dgaSplitkMatmulNoAlloc": (_i32, [_vp, _vp, _vp, _u32, _u32, _u32, _i32, _i32, _i32, _u32, _vp]),
     "dgaRunMmadCustom": (_i32, [_vp, _vp, _vp, _vp]),
     "dgaRunMmadRtc": (_i32, [_vp, _vp, _vp, _u32, _u32, _u32, _u32, _vp]),
@@ -101,6 +102,9 @@ def _load():
     # Rebuild when sources changed (a no-op hash check otherwise). No silent fallback: either the real
     # library loads or the import fails.
     path = _build.build()
+    # developer aid (tools/fp8_isolate.sh): a side build of the same sources with other -D flags; never a fallback -
+    # a path that does not load is an error
+    path = os.environ.get("DGA_B200_LIB", path)
     lib = ctypes.CDLL(path)
     for name, (restype, argtypes) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError here = header/library mismatch

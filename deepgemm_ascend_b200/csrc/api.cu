@@ -533,6 +533,27 @@ static int launch_splitk_inst(const DenseLaunch& L, const SmallMParams& sp, cuda
     return ACLNN_SUCCESS;
 }
 
+// The part of SmallMParams that follows from the plan alone.
+static void smallm_params(const DgaTilingPlan& p, SmallMParams& sp) {
+    const uint32_t m_pad = p.m1;
+    sp.m = p.m; sp.n = p.n; sp.k = p.k;
+    sp.m_pad = m_pad;
+    sp.split = p.splitkFactor;
+    sp.num_stages = p.stages;
+    sp.k_blocks = ceil_div(p.k, 64);
+    sp.idesc = make_idesc(128, m_pad, p.dtype == ACL_BF16 ? 1u : 0u, 0, 0);
+    uint32_t cols = 32;
+    while (cols < m_pad) cols <<= 1;
+    sp.tmem_cols = cols;
+    const int64_t pf = g_opt_splitk_prefetch.load(std::memory_order_relaxed);
+    sp.prefetch_kb = pf >= 0 ? uint32_t(pf) : 4u;
+    const int64_t ib = g_opt_splitk_batch.load(std::memory_order_relaxed);
+    sp.issue_batch = std::max<uint32_t>(1u, std::min<uint32_t>(ib > 0 ? uint32_t(ib) : 1u, p.stages));
+    static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
+    sp.trace = (dbg & 16) && p.blockDim * 12 <= kTraceWords ? trace_buffer() : nullptr;
+    sp.tiles_first = UINT32_MAX;
+}
+
 static int launch_splitk(DenseLaunch& L, cudaStream_t stream, void* workspace = nullptr) {
     const DgaTilingPlan& p = L.plan;
     const bool ws_mode = p.kernelSerial == DGA_KERNEL_DECODE_WS;
@@ -547,23 +568,9 @@ static int launch_splitk(DenseLaunch& L, cudaStream_t stream, void* workspace = 
         L.enc = L.eff;
     }
     SmallMParams sp{};
-    sp.m = p.m; sp.n = p.n; sp.k = p.k;
-    sp.m_pad = m_pad;
-    sp.split = p.splitkFactor;
-    sp.num_stages = p.stages;
-    sp.k_blocks = ceil_div(p.k, 64);
+    smallm_params(p, sp);
     sp.ldc = static_cast<uint32_t>(L.eff.ldd);
-    sp.idesc = make_idesc(128, m_pad, p.dtype == ACL_BF16 ? 1u : 0u, 0, 0);
-    uint32_t cols = 32;
-    while (cols < m_pad) cols <<= 1;
-    sp.tmem_cols = cols;
-    const int64_t pf = g_opt_splitk_prefetch.load(std::memory_order_relaxed);
-    sp.prefetch_kb = pf >= 0 ? uint32_t(pf) : 4u;
-    const int64_t ib = g_opt_splitk_batch.load(std::memory_order_relaxed);
-    sp.issue_batch = std::max<uint32_t>(1u, std::min<uint32_t>(ib > 0 ? uint32_t(ib) : 1u, p.stages));
     sp.out = L.eff.d;
-    static const uint32_t dbg = [] { const char* e = std::getenv("DGA_DEBUG_FLAGS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
-    sp.trace = (dbg & 16) && L.plan.blockDim * 12 <= kTraceWords ? trace_buffer() : nullptr;
     if (ws_mode) {
         // [split][m][pitch] fp32 slabs, the layout splitk_reduce_kernel adds up (the same reduce kernel as variant 5)
         if (sp.k_blocks < sp.split) {
@@ -624,6 +631,61 @@ static int launch_variant(DenseLaunch& L, cudaStream_t stream, void* workspace) 
     }
     set_error("kernel variant " + std::to_string(int(L.plan.kernelSerial)) + " is not built");
     return ACLNN_ERR_INNER_TILING_ERROR;
+}
+
+// ---- two decode GEMMs over the same activations in one launch (dgaDecodePairMatmul) ---------------------------
+template <typename OutT>
+static int launch_decode_pair_inst(const DgaTilingPlan& p, const CUtensorMap& w_first, const CUtensorMap& w_second,
+                                   const CUtensorMap& x, const SmallMParams& sp, cudaStream_t stream) {
+    auto kernel = gemm_smallm_pair_sm100_kernel<OutT>;
+    int rc = set_smem_attr(kernel, p.smemBytes);
+    if (rc != ACLNN_SUCCESS) return rc;
+    if (sp.split > 8) DGA_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(p.blockDim);
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.dynamicSmemBytes = p.smemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    fill_launch_attrs(cfg, attr, sp.split);
+    DGA_CUDA(cudaLaunchKernelEx(&cfg, kernel, w_first, w_second, x, sp));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return ACLNN_SUCCESS;
+}
+
+// `plan`: a finalised decode plan (kernelSerial 3) for the virtual shape m x (tiles_first + tiles_second) * 128 x k.
+static int launch_decode_pair(const DenseLaunch& first, const DenseLaunch& second, const DgaTilingPlan& plan,
+                              cudaStream_t stream) {
+    const DgaTilingPlan& p = plan;
+    const uint32_t m_pad = p.m1, n_first = first.plan.n, n_second = second.plan.n;
+    CUtensorMap w_first, w_second, x;
+    int rc = make_tmap_2d(&w_first, first.b, p.dtype, p.k, n_first, first.ldb, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc != ACLNN_SUCCESS) return rc;
+    rc = make_tmap_2d(&w_second, second.b, p.dtype, p.k, n_second, second.ldb, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc != ACLNN_SUCCESS) return rc;
+    rc = make_tmap_2d(&x, first.a, p.dtype, p.k, p.m, first.lda, 64, m_pad, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc != ACLNN_SUCCESS) return rc;
+    SmallMParams sp{};
+    smallm_params(p, sp);
+    sp.n = n_first;
+    sp.ldc = static_cast<uint32_t>(first.ldd);
+    sp.out = first.d;
+    sp.tiles_first = ceil_div(n_first, 128);
+    sp.n2 = n_second;
+    sp.ldc2 = static_cast<uint32_t>(second.ldd);
+    sp.out2 = second.d;
+    if (sp.k_blocks < sp.split || uint64_t(p.stages) * (16384 + m_pad * 128) < uint64_t(m_pad) * 512 ||
+        p.blockDim != (sp.tiles_first + ceil_div(n_second, 128)) * sp.split) {
+        set_error("decode pair plan infeasible for this shape");
+        return ACLNN_ERR_INNER_TILING_ERROR;
+    }
+    switch (p.outDtype) {
+        case ACL_BF16: return launch_decode_pair_inst<__nv_bfloat16>(p, w_first, w_second, x, sp, stream);
+        case ACL_FLOAT16: return launch_decode_pair_inst<__half>(p, w_first, w_second, x, sp, stream);
+        case ACL_FLOAT: return launch_decode_pair_inst<float>(p, w_first, w_second, x, sp, stream);
+    }
+    set_error("unsupported output dtype");
+    return ACLNN_ERR_PARAM_INVALID;
 }
 
 // rows x cols elements of `eb` bytes from a pitch of src_ld to a pitch of dst_ld (elements)
@@ -1132,6 +1194,45 @@ aclnnStatus dgaMatmulWithPlan(const aclTensor* self, const aclTensor* mat2, cons
         return ACLNN_ERR_PARAM_INVALID;
     }
     return launch_dense(L, static_cast<cudaStream_t>(stream), workspace);
+}
+
+// ---- two decode GEMMs that share their activations ---------------------------------------------------------------
+static void seed_plan(DgaTilingPlan& p, uint32_t m, uint32_t n, uint32_t k, int32_t dtype, int32_t outDtype,
+                      int32_t layoutTagB);
+aclnnStatus dgaDecodePairMatmul(const aclTensor* self, const aclTensor* mat2First, const aclTensor* outFirst,
+                                const aclTensor* mat2Second, const aclTensor* outSecond, aclrtStream stream) {
+    DenseLaunch first, second;
+    aclnnStatus rc = validate_dense(self, mat2First, outFirst, first);
+    if (rc == ACLNN_SUCCESS) rc = validate_dense(self, mat2Second, outSecond, second);
+    if (rc != ACLNN_SUCCESS) return rc;
+    const DgaTilingPlan& pf = first.plan;
+    if (pf.layoutTagB != 1 || second.plan.layoutTagB != 1 || pf.outDtype != second.plan.outDtype || pf.m > 128) {
+        set_error("dgaDecodePairMatmul: m <= 128, both weights stored [N,K], one output dtype (larger or row-major "
+                  "problems: two calls of the ordinary entry)");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    auto unaligned = [](const void* ptr, uint64_t ld) { return (reinterpret_cast<uintptr_t>(ptr) & 15) != 0 || (ld * 2) % 16 != 0; };
+    if (unaligned(first.a, first.lda) || unaligned(first.b, first.ldb) || unaligned(second.b, second.ldb)) {
+        set_error("dgaDecodePairMatmul: base pointers and row pitches of self and the weights must be 16-byte aligned");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    // one decode plan for the tiles of both weights: the selector's, or - where it would leave the decode kernel -
+    // the widest K split that keeps two CTAs per SM busy
+    const uint32_t tiles = ceil_div(pf.n, 128) + ceil_div(second.plan.n, 128);
+    DgaTilingPlan p;
+    seed_plan(p, pf.m, tiles * 128, pf.k, pf.dtype, pf.outDtype, 1);
+    rc = select_kernel(p);
+    if (rc != ACLNN_SUCCESS || p.kernelSerial != DGA_KERNEL_SPLITK) {
+        seed_plan(p, pf.m, tiles * 128, pf.k, pf.dtype, pf.outDtype, 1);
+        p.kernelSerial = DGA_KERNEL_SPLITK;
+        const uint32_t kb = ceil_div(pf.k, 64), slots = 2 * platform().smCount;
+        uint32_t split = 8;
+        while (split > 1 && (tiles * split > slots || split > kb)) split >>= 1;
+        p.splitkFactor = uint16_t(split);
+        rc = finalize_plan(p);
+        if (rc != ACLNN_SUCCESS) return rc;
+    }
+    return launch_decode_pair(first, second, p, static_cast<cudaStream_t>(stream));
 }
 
 // ---- N-sharded matmul with the gather of C fused into the epilogue ----------------------------------------------

@@ -45,6 +45,15 @@ struct Fp8Params {
     uint64_t hint_a, hint_b;   // L2 eviction hints of the operand loads (0 = normal), see GemmParams
 };
 
+// Bottleneck isolation, compile time only (tools/fp8_isolate.sh builds side libraries with -DDGA_FP8_ISOLATE=<flags>;
+// results are wrong with any of them): 32 the promotion warps only shake hands (no TMEM loads, no FMAs), 64 the MMA
+// warp does not wait for the promotion (nor the promotion for it), 128 TMEM loads but no FMAs, 256 no MMA instructions
+// (commits only).  A run-time flag in these loops costs 25 %.
+#ifndef DGA_FP8_ISOLATE
+#define DGA_FP8_ISOLATE 0
+#endif
+constexpr uint32_t kFp8Isolate = DGA_FP8_ISOLATE;
+
 struct Fp8Smem {
     uint32_t d_stage_bytes, a_stage_bytes, b_stage_bytes, sfb_pitch, off_d, off_a, off_b, off_sfb, off_bar, total;
 };
@@ -214,7 +223,7 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
                     ptx::mbar_wait(&full_bar[stage], phase);
 #pragma unroll
                     for (uint32_t h = 0; h < 2; ++h) {
-                        ptx::mbar_wait(&part_empty_bar[buf * 2 + h], par ^ 1);
+                        if constexpr (!(kFp8Isolate & 64)) ptx::mbar_wait(&part_empty_bar[buf * 2 + h], par ^ 1);
                         ptx::tc_fence_after();
                         if (ptx::elect_one()) {
                             const uint32_t a_lo = a_lo0 + stage * a_step;
@@ -224,7 +233,7 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
                             for (uint32_t k = 0; k < 4; ++k) {   // 4 x (K = 32 fp8 = 32 bytes) inside the 128 B atom
                                 const uint64_t a_desc = (static_cast<uint64_t>(hi) << 32) | (a_lo + k * 2);
                                 const uint64_t b_desc = (static_cast<uint64_t>(hi) << 32) | (b_lo + k * 2);
-                                ptx::mma_f8<kCta>(tmem_d, a_desc, b_desc, idesc, k != 0);
+                                if constexpr (!(kFp8Isolate & 256)) ptx::mma_f8<kCta>(tmem_d, a_desc, b_desc, idesc, k != 0);
                             }
                             ptx::mma_commit<kCta>(&part_full_bar[buf * 2 + h]);
                             if (h == 1) ptx::mma_commit<kCta>(&empty_bar[stage]);
@@ -321,7 +330,7 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
 #pragma unroll
                 for (uint32_t u = 0; u < kUnits; ++u)
                     s[u] = __uint_as_float((take_a[u] & __float_as_uint(pa)) | (~take_a[u] & __float_as_uint(pb)));
-                ptx::mbar_wait_addr(pf_addr, par);
+                if constexpr (!(kFp8Isolate & 64)) ptx::mbar_wait_addr(pf_addr, par);   // (64: both sides run free)
                 ptx::tc_fence_after();
                 // tcgen05.wait::ld waits for EVERY outstanding load of the thread, so loads cannot be pipelined one behind
                 // the other: each wait exposes a full TMEM round trip (~150 clocks with MMAs running).  Hence batches of
@@ -333,11 +342,16 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
                 for (uint32_t b = 0; b < kBatches; ++b) {
                     const uint32_t c0 = 64 * b;                       // first column of the batch inside the half
                     uint32_t v[64];
-                    if (c0 + 32 <= kHalf) ptx::tmem_ld_32x32(taddr + c0, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-                    else ptx::tmem_ld_32x16(taddr + c0, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
-                    if (c0 + 64 <= kHalf) ptx::tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
-                    else if (c0 + 48 <= kHalf) ptx::tmem_ld_32x16(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[16]>(&v[32]));
-                    ptx::tmem_ld_wait();
+                    if constexpr ((kFp8Isolate & 32) != 0) {
+#pragma unroll
+                        for (uint32_t j = 0; j < 64; ++j) v[j] = b;
+                    } else {
+                        if (c0 + 32 <= kHalf) ptx::tmem_ld_32x32(taddr + c0, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+                        else ptx::tmem_ld_32x16(taddr + c0, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
+                        if (c0 + 64 <= kHalf) ptx::tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+                        else if (c0 + 48 <= kHalf) ptx::tmem_ld_32x16(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[16]>(&v[32]));
+                        ptx::tmem_ld_wait();
+                    }
                     if (b + 1 == kBatches) {
                         // the whole half is in registers: hand its TMEM buffer back to the tensor core
                         ptx::tc_fence_before();
@@ -347,11 +361,15 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
                             else ptx::mbar_arrive_addr(pe_addr);
                         }
                     }
+                    if constexpr ((kFp8Isolate & (32 | 128)) != 0) {
+                        acc[c0] += __uint_as_float(v[0] ^ v[17] ^ v[34] ^ v[63]) * s[0];   // keeps the loads alive
+                    } else {
 #pragma unroll
-                    for (uint32_t j = 0; j < 64; j += 2) {
-                        if (c0 + j < kHalf)
-                            ptx::fma2(acc[c0 + j], acc[c0 + j + 1], __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
-                                      s[(c0 + j) / 16]);
+                        for (uint32_t j = 0; j < 64; j += 2) {
+                            if (c0 + j < kHalf)
+                                ptx::fma2(acc[c0 + j], acc[c0 + j + 1], __uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                          s[(c0 + j) / 16]);
+                        }
                     }
                 }
             };
@@ -361,12 +379,13 @@ gemm_fp8_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             const bool vec = (reinterpret_cast<uintptr_t>(p.sfa) & 15) == 0 && (p.sfa_ld & 3) == 0;
             float4 sa4 = load_scales4(sfa_row, 0, k_blocks, vec);
             float4 sa4n = sa4;
+            auto next_scales = [&](uint32_t kb) __attribute__((always_inline)) {   // at every fourth K block
+                if (kb != 0) sa4 = sa4n;
+                if (kb + 4 < k_blocks) sa4n = load_scales4(sfa_row, kb + 4, k_blocks, vec);
+            };
             for (uint32_t kb = 0; kb < k_blocks; ++kb, ++pc) {
                 const uint32_t ki = kb & 3;
-                if (ki == 0) {
-                    if (kb != 0) sa4 = sa4n;
-                    if (kb + 4 < k_blocks) sa4n = load_scales4(sfa_row, kb + 4, k_blocks, vec);
-                }
+                if (ki == 0) next_scales(kb);
                 promote(kb, pc % kNumBuf, (pc / kNumBuf) & 1, pick4(sa4, ki));
             }
 

@@ -40,6 +40,12 @@ struct SmallMParams {
     // tail, so the CTAs of the next launch on the stream move in as ours retire and start on their weights at once.
     float* partials;
     uint32_t ws_pitch;    // floats per workspace row (>= n)
+    // Pair launch (gemm_smallm_pair_sm100_kernel): two GEMMs that share X.  Tiles [0, tiles_first) belong to the first
+    // weight (n rows, output out / ldc), the rest to the second (n2 rows, output out2 / ldc2).
+    uint32_t tiles_first;
+    uint32_t n2;
+    uint32_t ldc2;
+    void* out2;
 };
 
 struct SmallMSmem {
@@ -68,10 +74,9 @@ __device__ __forceinline__ void store_out(OutT* p, float v) {
     else *p = __float2bfloat16_rn(v);
 }
 
-template <typename OutT>
-__global__ void __launch_bounds__(kNumThreads, 2)
-gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
-                         const SmallMParams p) {
+template <typename OutT, bool kPair>
+__device__ __forceinline__ void smallm_body(const CUtensorMap& tm_w_first, const CUtensorMap& tm_w_second,
+                                            const CUtensorMap& tm_x, const SmallMParams& p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
@@ -85,7 +90,12 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     const bool ws_mode = p.partials != nullptr;
     const uint32_t tile = blockIdx.x / split;
     const uint32_t rank = ws_mode ? blockIdx.x - tile * split : (split > 1 ? ptx::cluster_ctarank() : 0u);
-    const uint32_t n0 = tile * 128;
+    // which of the two GEMMs of a pair launch this cluster works for (uniform over the cluster)
+    const bool second = kPair && tile >= p.tiles_first;
+    const CUtensorMap& tm_w = second ? tm_w_second : tm_w_first;
+    const uint32_t n0 = (second ? tile - p.tiles_first : tile) * 128;
+    const uint32_t n_rows = second ? p.n2 : p.n;       // weight rows = output columns of this GEMM
+    const uint32_t ldc = second ? p.ldc2 : p.ldc;
     const uint32_t stages = p.num_stages;
     // this CTA's K blocks: [kb0, kb1)
     const uint32_t kb0 = static_cast<uint32_t>((static_cast<uint64_t>(rank) * p.k_blocks) / split);
@@ -195,7 +205,7 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
         __syncwarp();
     }
 
-    OutT* out = reinterpret_cast<OutT*>(p.out);
+    OutT* out = reinterpret_cast<OutT*>(second ? p.out2 : p.out);
     // Ownership of the activation rows inside a cluster: CTA d reduces rows [d * rows_per, (d + 1) * rows_per) ∩ [0, m)
     const uint32_t rows_per = (p.m + split - 1) / split;
     auto rows_of = [&](uint32_t d) { return d * rows_per >= p.m ? 0u : min(rows_per, p.m - d * rows_per); };
@@ -212,7 +222,7 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
         ptx::tc_fence_after();
         if (tr != nullptr && threadIdx.x == 128) tr[7] = clock64();
         const uint32_t taddr = tmem_base + (lane_base << 16);
-        const bool n_ok = n0 + row < p.n;
+        const bool n_ok = n0 + row < n_rows;
         // tmem_full fired: every MMA, hence every read of the ring, has completed; the ring is the staging tile now
         float* stage_out = reinterpret_cast<float*>(smem);
         // up to 64 activation columns per round: the TMEM loads go out back to back and share one wait
@@ -236,7 +246,7 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
 #pragma unroll
                 for (uint32_t j = 0; j < 64; ++j)
                     if (n_ok && j < left)
-                        store_out<OutT>(out + static_cast<uint64_t>(c + j) * p.ldc + n0 + row, __uint_as_float(v[j]));
+                        store_out<OutT>(out + static_cast<uint64_t>(c + j) * ldc + n0 + row, __uint_as_float(v[j]));
             } else {
 #pragma unroll
                 for (uint32_t j = 0; j < 64; ++j)
@@ -267,14 +277,14 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
             const uint32_t cg = (threadIdx.x & 31) * 4;
             const float* red = reinterpret_cast<const float*>(smem + L.off_red);
             const bool vec_ok = (reinterpret_cast<uintptr_t>(out) % (4 * sizeof(OutT)) == 0) &&
-                                (p.ldc % 4 == 0) && (n0 + 128 <= p.n);
+                                (ldc % 4 == 0) && (n0 + 128 <= n_rows);
             for (uint32_t r = threadIdx.x >> 5; r < my_rows; r += 8) {
                 float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
                 for (uint32_t s = 0; s < split; ++s) {
                     const float4 v = *reinterpret_cast<const float4*>(red + (s * rows_per + r) * 128 + cg);
                     acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
                 }
-                OutT* dst = out + static_cast<uint64_t>(rank * rows_per + r) * p.ldc + n0 + cg;
+                OutT* dst = out + static_cast<uint64_t>(rank * rows_per + r) * ldc + n0 + cg;
                 if (vec_ok) {
                     if constexpr (sizeof(OutT) == 4) {
                         *reinterpret_cast<float4*>(dst) = acc;
@@ -288,7 +298,7 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
                     const float a4[4] = {acc.x, acc.y, acc.z, acc.w};
 #pragma unroll
                     for (uint32_t j = 0; j < 4; ++j)
-                        if (n0 + cg + j < p.n) store_out<OutT>(dst + j, a4[j]);
+                        if (n0 + cg + j < n_rows) store_out<OutT>(dst + j, a4[j]);
                 }
             }
         }
@@ -301,6 +311,23 @@ gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_
     }
     if (warp == 2) ptx::tmem_dealloc<1>(tmem_base, p.tmem_cols);
     if (tr != nullptr && threadIdx.x == 0) { tr[10] = clock64(); tr[1] = ptx::globaltimer(); }
+}
+
+template <typename OutT>
+__global__ void __launch_bounds__(kNumThreads, 2)
+gemm_smallm_sm100_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
+                         const SmallMParams p) {
+    smallm_body<OutT, false>(tm_w, tm_w, tm_x, p);
+}
+
+// Two decode GEMMs over the same activations (gate / up, q / kv held as separate weights) in ONE launch: the fixed
+// cost of a launch (first round trip, reduction tail) is paid once for both weights' bytes.
+template <typename OutT>
+__global__ void __launch_bounds__(kNumThreads, 2)
+gemm_smallm_pair_sm100_kernel(const __grid_constant__ CUtensorMap tm_w_first,
+                              const __grid_constant__ CUtensorMap tm_w_second,
+                              const __grid_constant__ CUtensorMap tm_x, const SmallMParams p) {
+    smallm_body<OutT, true>(tm_w_first, tm_w_second, tm_x, p);
 }
 
 }  // namespace dga

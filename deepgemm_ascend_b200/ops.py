@@ -153,6 +153,33 @@ def matmul_with_plan(self, mat2, out, stream=None, **fields):
 _PLAN_WS = None
 
 
+class DecodePair:
+    """Two decode matmuls over the same activations in one launch (dgaDecodePairMatmul): out_first = self @ mat2_first,
+    out_second = self @ mat2_second, m <= 128, both weights stored [N, K] and passed as `w.t()`. For gate / up or
+    q / kv projections kept as separate weights. The tensor descriptions are built once; calling the object enqueues
+    the launch (CUDA-graph capturable, no workspace)."""
+
+    def __init__(self, self_t, mat2_first, out_first, mat2_second, out_second):
+        _require_cuda(self_t, mat2_first, out_first, mat2_second, out_second)
+        self._keep = (self_t, mat2_first, out_first, mat2_second, out_second)
+        self._desc = [acl_tensor(t) for t in self._keep]
+
+    def __call__(self, stream=None):
+        d = self._desc
+        check(lib.dgaDecodePairMatmul(ctypes.byref(d[0]), ctypes.byref(d[1]), ctypes.byref(d[2]), ctypes.byref(d[3]),
+                                      ctypes.byref(d[4]), _stream_ptr(stream)), "dgaDecodePairMatmul")
+        return self._keep[2], self._keep[4]
+
+
+def decode_pair_matmul(self, mat2_first, mat2_second, out_first=None, out_second=None, stream=None):
+    """One-shot form of DecodePair; allocates the outputs when they are not given."""
+    if out_first is None:
+        out_first = torch.empty((self.shape[0], mat2_first.shape[1]), dtype=self.dtype, device=self.device)
+    if out_second is None:
+        out_second = torch.empty((self.shape[0], mat2_second.shape[1]), dtype=self.dtype, device=self.device)
+    return DecodePair(self, mat2_first, out_first, mat2_second, out_second)(stream)
+
+
 def splitk_matmul_no_alloc(self, mat2, out, splitk_factor=0, stream=None):
     """out = self @ mat2 through dgaSplitkMatmulNoAlloc: the split-K + reduce variant with its fp32 slabs in the
     library's static device array (at most _lib.NO_ALLOC_SCRATCH_BYTES), no device allocation inside the call.

@@ -363,6 +363,50 @@ def test_concurrent_stream_k_launches_do_not_wait_on_each_other(dga):
         exe.close()
 
 
+# (m, n_first, n_second, k, dtype): decode pairs; ragged N on either side, one-tile weights, a K too short for the
+# selector's decode rule (128 x 8192 x 2048 goes to the persistent kernel: the pair entry forces its own split).
+# fp16 cases keep K short: an fp16 output of U(1, 10) inputs overflows beyond K ~ 2000.
+PAIR_CASES = [(1, 4096, 4096, 7168, torch.bfloat16), (16, 2048, 512, 7168, torch.bfloat16),
+              (64, 4096, 4096, 7168, torch.bfloat16), (64, 1536, 576, 1536, torch.float16),
+              (128, 1000, 520, 1992, torch.bfloat16), (50, 136, 2050, 1024, torch.float16),
+              (128, 4096, 4096, 2048, torch.bfloat16), (7, 128, 128, 128, torch.bfloat16)]
+
+
+@pytest.mark.parametrize("m,n_first,n_second,k,dtype", PAIR_CASES)
+def test_decode_pair_matches_fp64_oracle(dga, m, n_first, n_second, k, dtype):
+    """dgaDecodePairMatmul: two weights, one launch; both outputs against the oracle, and against the ordinary entry
+    at the same tolerance."""
+    a, b1 = _inputs(m, n_first, k, dtype, seed=5)
+    _, b2 = _inputs(m, n_second, k, dtype, seed=6)
+    ta = _to_dev(a, dtype)
+    w1, w2 = _to_dev(b1.T, dtype), _to_dev(b2.T, dtype)
+    o1 = torch.full((m, n_first), float("nan"), dtype=dtype, device=DEV)
+    o2 = torch.full((m, n_second), float("nan"), dtype=dtype, device=DEV)
+    pair = dga.DecodePair(ta, w1.t(), o1, w2.t(), o2)
+    before = dga.kernel_launch_count()
+    pair()
+    pair()   # repeatable
+    torch.cuda.synchronize()
+    assert dga.kernel_launch_count() - before == 2   # one kernel per pair
+    for out, b, w in ((o1, b1, w1), (o2, b2, w2)):
+        got = out.float().cpu().numpy()
+        assert np.isfinite(got).all()
+        assert orc.max_rel_err(got, orc.golden_fp64(a, b)) <= 1e-2
+        single = dga.catlass_dynamic_matmul(ta, w.t()).float().cpu().numpy()
+        assert orc.max_rel_err(got, single.astype(np.float64)) <= 1e-2
+
+
+def test_decode_pair_rejects_what_it_does_not_serve(dga):
+    ta = torch.ones((256, 512), dtype=torch.bfloat16, device=DEV)
+    w = torch.ones((256, 512), dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(dga.DgaError):    # m > 128
+        dga.decode_pair_matmul(ta, w.t(), w.t())
+    with pytest.raises(dga.DgaError):    # row-major [K, N] weight
+        dga.decode_pair_matmul(ta[:64], w.t(), torch.ones((512, 256), dtype=torch.bfloat16, device=DEV))
+    with pytest.raises(dga.DgaError):    # K extents differ
+        dga.decode_pair_matmul(ta[:64], w.t(), torch.ones((256, 256), dtype=torch.bfloat16, device=DEV).t())
+
+
 def test_executor_repeatable_and_graph_capturable(dga):
     a, b = _inputs(256, 512, 256, torch.bfloat16, seed=9)
     ta, w = _to_dev(a, torch.bfloat16), _to_dev(b.T, torch.bfloat16)

@@ -31,7 +31,7 @@ def main():
         assert ex[bn][0].path() == "promotion"
         if ref is None:
             ref = c[0].clone()
-        diff = (c[0].float() - ref.float()).abs().max().item() / ref.float().abs().max().item()
+        diff = (c[0].float() - ref.float()).abs().max().item() / max(ref.float().abs().max().item(), 1e-30)
         print("bn=%d: max |diff| / max |ref| against bn=%d: %.3e" % (bn, widths[0], diff), flush=True)
         total[bn] = 0.0
     rounds = 6

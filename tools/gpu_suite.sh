@@ -26,7 +26,7 @@ done
 python tools/show_bench.py $OUT/bench_*.json
 kernel_regex() {
   case $1 in
-    m1|m16|m64|m128) echo gemm_smallm ;;
+    m1|m16|m64|m128|m*pair|m*n*) echo gemm_smallm ;;
     fp8_fp32scales) echo gemm_fp8_sm100 ;;
     *) echo gemm_sm100 ;;
   esac
