@@ -63,13 +63,13 @@ def run_ours(args, rank, world):
         execs = [dga.Fp8Executor(a_bufs[i], sa[i], w_bufs[i], sw[i], c_bufs[i]) for i in range(sets)]
     else:
         a_bufs = [torch.randn((m, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
-        w_bufs = [torch.randn((n, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]  # [N,K]
+        w_rows = n // 2 if shape.get("pair") else n
+        w_bufs = [torch.randn((w_rows, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]  # [N,K]
         c_bufs = [torch.empty((m, n), device=dev, dtype=torch.bfloat16) for _ in range(sets)]
         if shape.get("pair"):
             # the two weights are separate allocations; C_first and C_second are the column halves of one [m, n] buffer
             h = n // 2
             w_second = [torch.randn((h, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
-            w_bufs = [torch.randn((h, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
             execs = [dga.DecodePair(a_bufs[i], w_bufs[i].t(), c_bufs[i][:, :h], w_second[i].t(), c_bufs[i][:, h:])
                      for i in range(sets)]
         elif workload == "moe":

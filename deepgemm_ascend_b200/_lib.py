@@ -102,9 +102,13 @@ def _load():
     # Rebuild when sources changed (a no-op hash check otherwise). No silent fallback: either the real
     # library loads or the import fails.
     path = _build.build()
-    # developer aid (tools/fp8_isolate.sh): a side build of the same sources with other -D flags; never a fallback -
-    # a path that does not load is an error
-    path = os.environ.get("DGA_B200_LIB", path)
+    # developer aid (tools/fp8_isolate.sh): a side build of the same sources with other -D flags, by NAME inside this
+    # package's lib directory (never an arbitrary path); never a fallback - a variant that does not load is an error
+    variant = os.environ.get("DGA_B200_LIB_VARIANT", "")
+    if variant:
+        if not variant.isalnum():
+            raise ImportError("DGA_B200_LIB_VARIANT must be alphanumeric, got %r" % variant)
+        path = os.path.join(os.path.dirname(path), "libdga_b200_%s.so" % variant)
     lib = ctypes.CDLL(path)
     for name, (restype, argtypes) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError here = header/library mismatch

@@ -20,7 +20,7 @@ fi
 OUT=${OUT:-gpurun_out/fp8_isolate}
 mkdir -p $OUT
 for f in ${FLAGS:-0 32 128 64 96 320 256}; do
-  lib=$PWD/$LIBDIR/libdga_b200_iso$f.so
-  [ $f = 0 ] && lib=$PWD/$LIBDIR/libdga_b200.so
-  DGA_B200_LIB=$lib timeout 300 python tools/fp8_tile_sweep.py ${SHAPE:-4096 7168 16384} 2>&1 | grep "TFLOP\|Error\|error" | sed "s/^/flags=$f  /" | tee -a $OUT/isolate.log
+  variant=iso$f
+  [ $f = 0 ] && variant=
+  DGA_B200_LIB_VARIANT=$variant timeout 300 python tools/fp8_tile_sweep.py ${SHAPE:-4096 7168 16384} 2>&1 | grep "TFLOP\|Error\|error" | sed "s/^/flags=$f  /" | tee -a $OUT/isolate.log
 done
