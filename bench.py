@@ -77,6 +77,8 @@ def workload_shape(name, world):
         return dict(m=16384, n=57344 // world, k=7168, dtype="bf16", n_total=57344, scaling="strong")
     if name in ("fp8", "fp8_fp32scales"):
         return dict(m=4096, n=7168, k=16384, dtype="fp8", n_total=7168 * world, scaling="weak")
+    if name == "moe256":   # the same MoE problem with the groups promised to start on multiples of 256 rows: pair tiles
+        return dict(m=8192, n=4096, k=7168, dtype="bf16", n_total=4096 * world, scaling="weak", groups=8, m_alignment=256)
     if name == "moe":
         return dict(m=8192, n=4096, k=7168, dtype="bf16", n_total=4096 * world, scaling="weak", groups=8)
     if re.fullmatch(r"m\d+pair", name):    # two decode GEMMs (N = 4096 each) sharing X in one launch: dgaDecodePairMatmul

@@ -72,16 +72,18 @@ def run_ours(args, rank, world):
             w_second = [torch.randn((h, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
             execs = [dga.DecodePair(a_bufs[i], w_bufs[i].t(), c_bufs[i][:, :h], w_second[i].t(), c_bufs[i][:, h:])
                      for i in range(sets)]
-        elif workload == "moe":
+        elif shape.get("groups"):
             g = shape["groups"]
             w_bufs = [torch.randn((g, n, k), device=dev, dtype=torch.bfloat16, generator=gen) for _ in range(sets)]
             index = torch.arange(g, device=dev, dtype=torch.int32).repeat_interleave(m // g)
-            execs = [dga.MGroupedExecutor(a_bufs[i], w_bufs[i], index, c_bufs[i]) for i in range(sets)]
+            execs = [dga.MGroupedExecutor(a_bufs[i], w_bufs[i], index, c_bufs[i], m_alignment=shape.get("m_alignment", 128))
+                     for i in range(sets)]
         else:
             execs = [dga.Executor(a_bufs[i], w_bufs[i].t(), c_bufs[i]) for i in range(sets)]   # phase 1, once per set
     plan = dga.select_kernel(m, n, k, use_cache=True) if not fp8 else {"kernelSerial": 0}
-    if workload == "moe":
-        plan = {"kernelSerial": 0, "ctaGroup": 1, "m1": 128}
+    if shape.get("groups"):
+        pair = shape.get("m_alignment", 128) == 256
+        plan = {"kernelSerial": 0, "ctaGroup": 2 if pair else 1, "m1": 256 if pair else 128}
 
     stream = torch.cuda.current_stream()
     graph = None
@@ -146,7 +148,7 @@ def run_ours(args, rank, world):
 
     # ---- e2e: host buffers in, host buffer out, through the public operator call
     e2e = e2e_run(dga, dev, m, n, k, steps=max(3, min(args.steps, 20)), flops=flops, world=world, dist=dist, fp8=fp8,
-                  groups=shape.get("groups", 0), pair=bool(shape.get("pair")))
+                  groups=shape.get("groups", 0), pair=bool(shape.get("pair")), m_alignment=shape.get("m_alignment", 128))
 
     # ---- optional: all-gather of C over NVLink (only when the caller needs the full output)
     gather = None
@@ -309,7 +311,7 @@ def _e2e_rates(e2e, ms_per_step, world, dev, dist):
     return e2e
 
 
-def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False, groups=0, pair=False):
+def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False, groups=0, pair=False, m_alignment=128):
     """Same metric end to end: every step copies its A and W from pinned host memory to the device, calls the
     operator and copies C back to pinned host memory, all inside the timed region.  The three legs run on three
     streams over a ring of 2 device buffer sets, so the copies of step i+1 and i-1 overlap the GEMM of step i
@@ -352,7 +354,7 @@ def e2e_run(dga, dev, m, n, k, steps, flops, world, dist, fp8=False, groups=0, p
             if fp8:
                 dga.fp8_block_scaled_matmul(da[i], dsa[i], dw[i], dsw[i], out=dc[i])
             elif groups:
-                dga.m_grouped_matmul(da[i], dw[i], index, out=dc[i])
+                dga.m_grouped_matmul(da[i], dw[i], index, out=dc[i], m_alignment=m_alignment)
             elif pair:   # the two weights are the row halves of the host buffer, the two outputs the column halves
                 h = n // 2
                 dga.decode_pair_matmul(da[i], dw[i][:h].t(), dw[i][h:].t(), dc[i][:, :h], dc[i][:, h:])

@@ -74,6 +74,7 @@ SIGNATURES = {
     "dgaGetPlatformInfo": (_i32, [_P(PlatformInfo)]),
     "dgaSetPlatformInfo": (_i32, [_P(PlatformInfo)]),
     "dgaMatmulWithPlan": (_i32, [_P(AclTensor), _P(AclTensor), _P(AclTensor), _P(TilingPlan), _vp, _u64, _vp]),
+    "dgaSetExecutorGroupAlignment": (_i32, [_vp, _u32]),
     "dgaDecodePairMatmul": (_i32, [_P(AclTensor)] * 5 + [_vp]),
     "dgaSplitkMatmulNoAlloc": (_i32, [_vp, _vp, _vp, _u32, _u32, _u32, _i32, _i32, _i32, _u32, _vp]),
     "dgaRunMmadCustom": (_i32, [_vp, _vp, _vp, _vp]),

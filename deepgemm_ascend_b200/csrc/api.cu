@@ -491,9 +491,19 @@ static int launch_common(DenseLaunch& L, cudaStream_t stream, void* workspace) {
         gp.tiles_per_batch = gp.dp_tiles;
         gp.group_index = L.group_index;
         if (mode_is_batched(L.mode)) gp.dp_tiles *= L.batch;
-        if (cta != 1 || p.kernelSerial == DGA_KERNEL_STREAMK) {
-            set_error("batched / grouped launches use single-CTA whole tiles");
+        if ((cta != 1 && L.mode == kModeBatched) || p.kernelSerial == DGA_KERNEL_STREAMK) {
+            set_error("batched launches use single-CTA whole tiles; grouped launches whole tiles");
             return ACLNN_ERR_INNER_TILING_ERROR;
+        }
+        if (cta == 2 && p.layoutTagB == 1) {   // pair tiles: groups aligned to 256 rows (dgaSetExecutorGroupAlignment)
+            if (L.mode == kModeMGrouped && p.outDtype == ACL_BF16)
+                return launch_common_inst<2, __nv_bfloat16, false, kModeMGrouped>(L, gp, stream);
+            if (L.mode == kModeMGrouped && p.outDtype == ACL_FLOAT16)
+                return launch_common_inst<2, __half, false, kModeMGrouped>(L, gp, stream);
+            if (L.mode == kModeMasked && p.outDtype == ACL_BF16)
+                return launch_common_inst<2, __nv_bfloat16, false, kModeMasked>(L, gp, stream);
+            if (L.mode == kModeMasked && p.outDtype == ACL_FLOAT16)
+                return launch_common_inst<2, __half, false, kModeMasked>(L, gp, stream);
         }
         if (L.mode == kModeBatched && p.layoutTagB == 0 && p.outDtype == ACL_FLOAT)
             return launch_common_inst<1, float, true, kModeBatched>(L, gp, stream);
@@ -1531,6 +1541,32 @@ aclnnStatus dgaMGroupedMatmul(void* workspace, uint64_t workspaceSize, aclOpExec
     return rc;
 }
 
+static int plan_slab_tiles(DgaTilingPlan& p, uint32_t slabs_of_tiles, uint32_t cta);
+// The caller's promise about a grouped executor's row layout, made between phase 1 and phase 2.  rows = 256: every
+// group of the contiguous layout starts on a multiple of 256 rows (padding blocks, index -1, fill each group up) resp.
+// Mmax of the masked layout is a multiple of 256: the launch uses 256-row CTA-pair tiles (cta_group::2, the weight
+// tile shared by the pair) instead of 128-row single-CTA tiles.  rows = 128 returns to the default.  A contiguous
+// layout that breaks the promise gives wrong rows in the blocks that share a pair with another group.
+aclnnStatus dgaSetExecutorGroupAlignment(aclOpExecutor* executor, uint32_t rows) {
+    if (executor == nullptr || executor->is_fp8 ||
+        (executor->dense.mode != kModeMGrouped && executor->dense.mode != kModeMasked)) {
+        set_error("not a grouped-matmul executor");
+        return ACLNN_ERR_PARAM_NULLPTR;
+    }
+    DenseLaunch& L = executor->dense;
+    if ((rows != 128 && rows != 256) || L.plan.m % rows != 0) {
+        set_error("group alignment is 128 or 256 rows and must divide the row count (" + std::to_string(L.plan.m) + ")");
+        return ACLNN_ERR_PARAM_INVALID;
+    }
+    const DgaTilingPlan keep = L.plan;
+    seed_plan(L.plan, keep.m, keep.n, keep.k, keep.dtype, keep.outDtype, keep.layoutTagB);
+    L.plan.strideA = keep.strideA; L.plan.strideB = keep.strideB; L.plan.strideC = keep.strideC;
+    const int rc = plan_slab_tiles(L.plan, L.mode == kModeMasked ? L.batch : 1u, rows / 128);
+    if (rc != ACLNN_SUCCESS) L.plan = keep;
+    L.encoded = false;   // the weight box depends on the CTA group
+    return rc;
+}
+
 // ---- host tiling -------------------------------------------------------------------------------------
 static void seed_plan(DgaTilingPlan& p, uint32_t m, uint32_t n, uint32_t k, int32_t dtype, int32_t outDtype,
                       int32_t layoutTagB) {
@@ -1614,28 +1650,32 @@ static aclnnStatus framework_gemm(const void* x, const void* y, void* z, uint32_
 }
 
 // Single-CTA tile of a batched / grouped launch: widest N tile whose wave count over all SMs is minimal.
-static int plan_single_cta(DgaTilingPlan& p, uint32_t slabs_of_tiles) {
+// cta = 2: pair tiles of 256 rows (grouped launches whose groups are aligned to 256 rows).
+static int plan_slab_tiles(DgaTilingPlan& p, uint32_t slabs_of_tiles, uint32_t cta) {
     const uint32_t step = p.layoutTagB == 0 ? 64 : 32;
+    const uint32_t units = platform().smCount / cta;   // CTAs or CTA pairs
     uint32_t best_n1 = 0;
     uint64_t best_cost = ~0ull;
     for (uint32_t n1 = 256; n1 >= 64; n1 -= step) {
-        const uint64_t tiles = uint64_t(ceil_div(p.m, 128)) * ceil_div(p.n, n1) * slabs_of_tiles;
-        const uint64_t waves = (tiles + platform().smCount - 1) / platform().smCount;
+        const uint64_t tiles = uint64_t(ceil_div(p.m, 128 * cta)) * ceil_div(p.n, n1) * slabs_of_tiles;
+        const uint64_t waves = (tiles + units - 1) / units;
         const uint64_t cost = waves * (n1 + 24);   // + per-tile overhead in column units
         if (cost < best_cost) { best_cost = cost; best_n1 = n1; }
     }
     p.kernelSerial = DGA_KERNEL_COMMON;
-    p.ctaGroup = 1;
+    p.ctaGroup = uint8_t(cta);
+    p.clusterShape = 0;
     p.n1 = uint16_t(best_n1);
     p.stages = 0;
     p.splitkFactor = 1;
     p.paddingTagA = p.paddingTagB = p.paddingTagC = 0;
     int rc = finalize_plan(p);
     if (rc != ACLNN_SUCCESS) return rc;
-    const uint64_t tiles = uint64_t(ceil_div(p.m, 128)) * ceil_div(p.n, p.n1) * slabs_of_tiles;
-    p.blockDim = uint32_t(std::min<uint64_t>(tiles, platform().smCount));
+    const uint64_t tiles = uint64_t(ceil_div(p.m, 128 * cta)) * ceil_div(p.n, p.n1) * slabs_of_tiles;
+    p.blockDim = uint32_t(std::min<uint64_t>(tiles, units)) * cta;
     return ACLNN_SUCCESS;
 }
+static int plan_single_cta(DgaTilingPlan& p, uint32_t slabs_of_tiles) { return plan_slab_tiles(p, slabs_of_tiles, 1); }
 
 static int plan_batched(DgaTilingPlan& p, uint32_t batch, uint32_t m, uint32_t n, uint32_t k) {
     seed_plan(p, m, n, k, ACL_BF16, ACL_FLOAT, /*layoutTagB=*/0);

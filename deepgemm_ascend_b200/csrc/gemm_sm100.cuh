@@ -254,6 +254,14 @@ __host__ __device__ inline SmemLayout make_smem_layout(uint32_t d_stage_bytes, u
 constexpr int kModePlain = 0, kModeBatched = 1, kModeMGrouped = 2, kModeSplitK = 3, kModeMasked = 4;
 // batched addressing (third tensor-map coordinate = tile / tiles_per_batch)
 constexpr bool mode_is_batched(int mode) { return mode == kModeBatched || mode == kModeMasked; }
+// Group of a tile in the M-grouped contiguous layout: the group of its first live 128-row block, -1 when every block
+// is padding.  Pair tiles (256 rows) are only planned when the caller has promised that groups start on multiples of
+// 256 rows, so the two blocks never belong to different groups (one of them may be padding).
+__device__ __forceinline__ int32_t pair_group(const GemmParams& p, uint32_t m0, int cta) {
+    int32_t g = __ldg(p.group_index + m0);
+    if (cta == 2 && g < 0 && m0 + kBlockM < p.m) g = __ldg(p.group_index + m0 + kBlockM);
+    return g;
+}
 // Turns the iterator's item into (tile, K-block range, slab = third coordinate of the 3-D maps).
 template <int kMode>
 __device__ __forceinline__ void resolve_item(const GemmParams& p, WorkItem& w, uint32_t& slab) {
@@ -294,8 +302,9 @@ __device__ __forceinline__ void
 gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensorMap& tm_d, const CUtensorMap& tm_sfa,
                 const CUtensorMap& tm_sfb, const PeerMaps& peers, const GemmParams& p) {
     static_assert(!(kMx && kBMn), "block-scaled fp8 wants K-major operands");
-    static_assert(kMode == kModePlain || kMode == kModeSplitK || (kCta == 1 && !kMx),
-                  "batched / grouped modes are single-CTA, 16-bit");
+    static_assert(kMode == kModePlain || kMode == kModeSplitK || !kMx, "batched / grouped modes are 16-bit");
+    static_assert(kCta == 1 || kMode != kModeBatched, "the framework's batched launch uses single-CTA tiles");
+    static_assert(kCta == 1 || !kBMn || kMode == kModePlain || kMode == kModeSplitK, "grouped pair tiles want [G,N,K] weights");
     static_assert(kMode != kModeSplitK || (sizeof(OutT) == 4 && !kMx), "split-K slices leave fp32 partial tiles");
     static_assert(!kSk || (kMode == kModePlain && !kMx), "stream-K is a variant of the plain 16-bit kernel");
     static_assert(!kMc || (kCta == 2 && kMode == kModePlain && !kSk && !kMx), "the multicast cluster is two whole-tile 16-bit CTA pairs");
@@ -396,11 +405,11 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             const int32_t m_idx = static_cast<int32_t>(mb * (kBlockM * kCta) + cta_rank * kBlockM);
             const int32_t n_idx = static_cast<int32_t>(nb * p.block_n + cta_rank * load_n);
             if constexpr (kMode == kModeMGrouped) {
-                z = __ldg(p.group_index + m_idx);
+                z = pair_group(p, mb * (kBlockM * kCta), kCta);
                 if (z < 0) continue;   // every role skips the same blocks
             }
-            if constexpr (kMode == kModeMasked) {
-                if (m_idx >= __ldg(p.group_index + slab)) continue;
+            if constexpr (kMode == kModeMasked) {   // (pair tiles: decided by the pair's FIRST row block)
+                if (static_cast<int32_t>(mb * (kBlockM * kCta)) >= __ldg(p.group_index + slab)) continue;
             }
             for (uint32_t kb = w.kb0; kb < w.kb1; ++kb) {
                 ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -437,11 +446,15 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                             ptx::tma_load_2d_pair_multicast(&tm_a, &full_bar[stage], sa + pair * (kBlockM / 2) * kBlockKBytes,
                                                             k_idx, m_idx + static_cast<int32_t>(pair * (kBlockM / 2)),
                                                             static_cast<uint16_t>(0x5u << cta_rank), hint_a);
+                        else if constexpr (mode_is_batched(kMode))
+                            ptx::tma_load_3d_pair(&tm_a, &full_bar[stage], sa, k_idx, m_idx, z, hint_a);
                         else
                             ptx::tma_load_2d_pair(&tm_a, &full_bar[stage], sa, k_idx, m_idx, hint_a);
                         if constexpr (kBMn) {
                             for (uint32_t j = 0; j < load_n / 64; ++j)
                                 ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb + j * 8192, n_idx + j * 64, k_idx, hint_b);
+                        } else if constexpr (kMode == kModeMGrouped || kMode == kModeMasked) {
+                            ptx::tma_load_3d_pair(&tm_b, &full_bar[stage], sb, k_idx, n_idx, z, hint_b);   // weight of group z
                         } else {
                             ptx::tma_load_2d_pair(&tm_b, &full_bar[stage], sb, k_idx, n_idx, hint_b);
                         }
@@ -495,8 +508,9 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                 if constexpr (kMode == kModeMGrouped || kMode == kModeMasked) {
                     uint32_t mb, nb;
                     tile_coords(p, w.tile, mb, nb);
-                    const int32_t g = __ldg(p.group_index + (kMode == kModeMasked ? slab_of_item : mb * kBlockM));
-                    if (kMode == kModeMasked ? static_cast<int32_t>(mb * kBlockM) >= g : g < 0) { --iter; continue; }
+                    const int32_t g = kMode == kModeMasked ? __ldg(p.group_index + slab_of_item)
+                                                           : pair_group(p, mb * (kBlockM * kCta), kCta);
+                    if (kMode == kModeMasked ? static_cast<int32_t>(mb * (kBlockM * kCta)) >= g : g < 0) { --iter; continue; }
                 }
                 if constexpr (kKs) {
                     w.kb0 = pair * (p.k_blocks / 2);
@@ -604,12 +618,19 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
             if constexpr (kMc) nb = nb * 2 + pair;
             const uint32_t m0 = mb * (kBlockM * kCta) + cta_rank * kBlockM;
             const uint32_t n0 = nb * p.block_n;
+            // pair tiles: the tile is worked on when either row block is live; a CTA whose own block is padding (or
+            // starts past the group's valid rows) takes part in the TMEM handshake but stores nothing
+            bool own_rows_live = true;
             if constexpr (kMode == kModeMGrouped) {
-                if (__ldg(p.group_index + m0) < 0) { --iter; continue; }
+                if (pair_group(p, mb * (kBlockM * kCta), kCta) < 0) { --iter; continue; }
+                own_rows_live = __ldg(p.group_index + m0) >= 0;
             }
             if constexpr (kMode == kModeMasked) {
-                if (static_cast<int32_t>(m0) >= __ldg(p.group_index + slab)) { --iter; continue; }
+                const int32_t valid = __ldg(p.group_index + slab);
+                if (static_cast<int32_t>(mb * (kBlockM * kCta)) >= valid) { --iter; continue; }
+                own_rows_live = static_cast<int32_t>(m0) < valid;
             }
+            const uint32_t m0_store = own_rows_live ? m0 : p.m;   // store_chunk skips rows at or beyond p.m
             const uint32_t as = iter & 1, aphase = (iter >> 1) & 1;
             // chunks that intersect the matrix (TMA clips a partial last one)
             const uint32_t n_left = p.n - n0;
@@ -682,7 +703,7 @@ gemm_sm100_body(const CUtensorMap& tm_a, const CUtensorMap& tm_b, const CUtensor
                     ptx::tmem_ld_32x32(taddr + chunk_col(c), v);
                     ptx::tmem_ld_wait();
                     if (c + 1 == chunks) release_tmem();
-                    store_chunk(v, m0, n0 + chunk_col(c), c, c + 1 == chunks);
+                    store_chunk(v, m0_store, n0 + chunk_col(c), c, c + 1 == chunks);
                 }
             } else {
                 // ---- stream-K slice.  Slices 0 .. S-2 of a tile ("givers") leave their fp32 partial in their

@@ -263,6 +263,16 @@ __device__ __forceinline__ void tma_load_3d(const void* desc, uint64_t* bar, voi
         :: "r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(desc)), "r"(smem_u32(bar)),
            "r"(c0), "r"(c1), "r"(c2), "l"(hint) : "memory");
 }
+// 3-D tile load issued by either CTA of a pair (bytes complete on the leader's barrier, see tma_load_2d_pair).
+__device__ __forceinline__ void tma_load_3d_pair(const void* desc, uint64_t* bar, void* smem,
+                                                 int32_t c0, int32_t c1, int32_t c2, uint64_t hint = kEvictNormal) {
+    uint32_t bar_addr = smem_u32(bar) & 0xFEFFFFFFu;
+    asm volatile(
+        "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+        " [%0], [%1, {%3, %4, %5}], [%2], %6;"
+        :: "r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(desc)), "r"(bar_addr),
+           "r"(c0), "r"(c1), "r"(c2), "l"(hint) : "memory");
+}
 // L2 prefetch of one box: warms the (device-coherent) L2 only, no shared-memory destination and no completion
 // to wait for, so it may be issued for data another grid is still producing.
 __device__ __forceinline__ void tma_prefetch_2d(const void* desc, int32_t c0, int32_t c1) {

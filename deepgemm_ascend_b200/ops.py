@@ -241,9 +241,19 @@ def nshard_range(n, world_size, rank):
 
 
 # ---- M-grouped contiguous matmul (MoE; DeepGEMM m_grouped_gemm_nt_contiguous semantics) -------------------------
-def m_grouped_matmul(self, weight, group_index, out=None, stream=None):
+def _set_group_alignment(ex, m_alignment):
+    if m_alignment != 128:
+        rc = lib.dgaSetExecutorGroupAlignment(ex, int(m_alignment))
+        if rc != 0:
+            destroy_executor(ex)
+            check(rc, "dgaSetExecutorGroupAlignment")
+
+
+def m_grouped_matmul(self, weight, group_index, out=None, stream=None, m_alignment=128):
     """out[i,:] = self[i,:] @ weight[group_index[i]].T; self [M_total,K], weight [G,N,K], group_index int32 [M_total]
-    (constant over every 128-row block, -1 = padding block left unwritten), M_total % 128 == 0."""
+    (constant over every 128-row block, -1 = padding block left unwritten), M_total % 128 == 0.
+    m_alignment=256: the caller's promise that every group starts on a multiple of 256 rows; the launch then uses
+    256-row CTA-pair tiles (dgaSetExecutorGroupAlignment)."""
     _require_cuda(self, weight, group_index)
     if out is None:
         out = torch.empty((self.shape[0], weight.shape[1]), dtype=self.dtype, device=self.device)
@@ -253,13 +263,15 @@ def m_grouped_matmul(self, weight, group_index, out=None, stream=None):
     check(lib.dgaMGroupedMatmulGetWorkspaceSize(ctypes.byref(a), ctypes.byref(w), ctypes.byref(g), ctypes.byref(c),
                                                 ctypes.byref(ws), ctypes.byref(ex)),
           "dgaMGroupedMatmulGetWorkspaceSize")
+    _set_group_alignment(ex, m_alignment)
     check(lib.dgaMGroupedMatmul(ctypes.c_void_p(None), 0, ex, _stream_ptr(stream)), "dgaMGroupedMatmul")
     return out
 
 
-def m_grouped_matmul_masked(self, weight, masked_m, out=None, stream=None):
+def m_grouped_matmul_masked(self, weight, masked_m, out=None, stream=None, m_alignment=128):
     """out[g,i,:] = self[g,i,:] @ weight[g].T for i < masked_m[g]; self [G,Mmax,K], weight [G,N,K], masked_m int32 [G]
-    on the device (no host sync). Whole 128-row blocks past masked_m[g] are skipped and left unwritten."""
+    on the device (no host sync). Whole 128-row blocks past masked_m[g] are skipped and left unwritten.
+    m_alignment=256 (Mmax % 256 == 0): 256-row CTA-pair tiles, worth it when most groups hold more than 128 rows."""
     _require_cuda(self, weight, masked_m)
     if out is None:
         out = torch.empty((self.shape[0], self.shape[1], weight.shape[1]), dtype=self.dtype, device=self.device)
@@ -269,6 +281,7 @@ def m_grouped_matmul_masked(self, weight, masked_m, out=None, stream=None):
     check(lib.dgaMGroupedMaskedMatmulGetWorkspaceSize(ctypes.byref(a), ctypes.byref(w), ctypes.byref(g),
                                                       ctypes.byref(c), ctypes.byref(ws), ctypes.byref(ex)),
           "dgaMGroupedMaskedMatmulGetWorkspaceSize")
+    _set_group_alignment(ex, m_alignment)
     check(lib.dgaMGroupedMatmul(ctypes.c_void_p(None), 0, ex, _stream_ptr(stream)), "dgaMGroupedMatmul")
     return out
 
@@ -276,7 +289,7 @@ def m_grouped_matmul_masked(self, weight, masked_m, out=None, stream=None):
 class MGroupedExecutor:
     """Repeatable grouped-matmul plan: phase 1 once, phase 2 per call."""
 
-    def __init__(self, self_t, weight, group_index, out):
+    def __init__(self, self_t, weight, group_index, out, m_alignment=128):
         _require_cuda(self_t, weight, group_index, out)
         self._keep = (self_t, weight, group_index, out)
         ws = ctypes.c_uint64(0)
@@ -285,6 +298,7 @@ class MGroupedExecutor:
         check(lib.dgaMGroupedMatmulGetWorkspaceSize(ctypes.byref(a), ctypes.byref(w), ctypes.byref(g), ctypes.byref(c),
                                                     ctypes.byref(ws), ctypes.byref(ex)),
               "dgaMGroupedMatmulGetWorkspaceSize")
+        _set_group_alignment(ex, m_alignment)
         check(lib.dgaSetExecutorRepeatable(ex), "dgaSetExecutorRepeatable")
         self._ex = ex
 

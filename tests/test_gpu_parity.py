@@ -602,6 +602,79 @@ def test_m_grouped_masked_matches_oracle(dga, groups, m_max, n, k, dtype):
         assert np.all(got[g, first_skipped:] == 768.0)
 
 
+@pytest.mark.parametrize("groups,n,k,dtype", [(4, 512, 256, torch.bfloat16), (7, 1000, 520, torch.bfloat16),
+                                                (3, 384, 1024, torch.float16)])
+def test_m_grouped_pair_tiles_matches_oracle(dga, groups, n, k, dtype):
+    """m_alignment=256: every group occupies a multiple of 256 rows (its tail filled with padding blocks, index -1),
+    the launch uses 256-row CTA-pair tiles. A pair may hold one live block and one padding block, in either order
+    (a group of 128 live rows; a leading padding block), or two padding blocks: padding is never written."""
+    rng = np.random.RandomState(groups * 7 + n + k)
+    index = [-1] * 128 + [0] * 128                      # padding FIRST inside a pair, then group 0's only block
+    for g in range(1, groups):
+        live = int(rng.randint(0, 5))                    # live 128-row blocks of this group (0: the group is empty)
+        slot = -(-live // 2) * 2                         # padded to whole pairs
+        index += [g] * (128 * live) + [-1] * (128 * (slot - live))
+        if g == 2:
+            index += [-1] * 256                          # a pair of padding blocks
+    index = np.array(index, dtype=np.int32)
+    m_total = index.size
+    assert m_total % 256 == 0
+    a, _ = _inputs(m_total, 8, k, dtype, seed=2)
+    w = np.stack([_inputs(8, n, k, dtype, seed=20 + g)[1].T for g in range(groups)])   # [G, N, K]
+    ta, tw, ti = _to_dev(a, dtype), _to_dev(w, dtype), torch.from_numpy(index).to(DEV)
+    out = torch.full((m_total, n), 768.0, dtype=dtype, device=DEV)
+    before = dga.kernel_launch_count()
+    dga.m_grouped_matmul(ta, tw, ti, out=out, m_alignment=256)
+    torch.cuda.synchronize()
+    assert dga.kernel_launch_count() - before == 1
+    got = out.float().cpu().numpy()
+    ref = orc.m_grouped_golden_fp64(a, w, index)
+    live = index >= 0
+    assert orc.max_rel_err(got[live], ref[live]) <= (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7)
+    assert np.all(got[~live] == 768.0)                   # padding blocks are left untouched
+    # the same problem through the default single-CTA tiles: identical sums (same K order per row)
+    out128 = torch.full((m_total, n), 768.0, dtype=dtype, device=DEV)
+    dga.m_grouped_matmul(ta, tw, ti, out=out128)
+    torch.cuda.synchronize()
+    assert np.array_equal(got, out128.float().cpu().numpy())
+    ex = dga.MGroupedExecutor(ta, tw, ti, out, m_alignment=256)   # repeatable form
+    out.fill_(768.0)
+    ex(); ex()
+    torch.cuda.synchronize()
+    assert np.array_equal(got, out.float().cpu().numpy())
+    ex.close()
+    with pytest.raises(dga.DgaError):                    # 384 rows are not a multiple of 256
+        dga.m_grouped_matmul(ta[:384], tw, ti[:384], m_alignment=256)
+
+
+@pytest.mark.parametrize("groups,m_max,n,k,dtype", [(4, 256, 512, 256, torch.bfloat16),
+                                                      (6, 512, 1000, 520, torch.bfloat16),
+                                                      (3, 768, 384, 1024, torch.float16)])
+def test_m_grouped_masked_pair_tiles_matches_oracle(dga, groups, m_max, n, k, dtype):
+    rng = np.random.RandomState(groups + m_max + n + k)
+    masked = rng.randint(0, m_max + 1, size=groups).astype(np.int32)
+    masked[0], masked[-1] = 0, m_max                    # an empty group and a full one
+    if groups > 2:
+        masked[1] = 100                                  # only the first block of the first pair is live
+    a = np.stack([_inputs(m_max, 8, k, dtype, seed=60 + g)[0] for g in range(groups)])       # [G, Mmax, K]
+    w = np.stack([_inputs(8, n, k, dtype, seed=70 + g)[1].T for g in range(groups)])         # [G, N, K]
+    ta, tw = _to_dev(a, dtype), _to_dev(w, dtype)
+    out = torch.full((groups, m_max, n), 768.0, dtype=dtype, device=DEV)
+    before = dga.kernel_launch_count()
+    dga.m_grouped_matmul_masked(ta, tw, torch.from_numpy(masked).to(DEV), out=out, m_alignment=256)
+    torch.cuda.synchronize()
+    assert dga.kernel_launch_count() - before == 1
+    got = out.float().cpu().numpy()
+    ref = orc.m_grouped_masked_golden_fp64(a, w, masked)
+    tol = 2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7
+    for g in range(groups):
+        rows = int(masked[g])
+        if rows:
+            assert orc.max_rel_err(got[g, :rows], ref[g, :rows]) <= tol
+        first_skipped = -(-rows // 128) * 128            # whole blocks past masked_m are left untouched
+        assert np.all(got[g, first_skipped:] == 768.0)
+
+
 # ---- seeded fuzz over shapes, layouts, dtypes and plans (edge cases: tiny, ragged, odd pitches) ------------------------
 def _fuzz_cases(count=48, seed=20261104):
     rng = np.random.RandomState(seed)

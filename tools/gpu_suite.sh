@@ -12,7 +12,7 @@
 OUT=${OUT:-gpurun_out/suite}
 STEPS=${STEPS:-30}
 WARMUP=${WARMUP:-5}
-WORKLOADS=${WORKLOADS-"m1 m16 m64 m128 m64pair m128pair m256 m512 m2048 m8192 fp8 fp8_fp32scales moe repack config5"}
+WORKLOADS=${WORKLOADS-"m1 m16 m64 m128 m64pair m128pair m256 m512 m2048 m8192 fp8 fp8_fp32scales moe moe256 repack config5"}
 mkdir -p $OUT
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw,memory.total --format=csv > $OUT/gpu.txt 2>&1
 if [ "${TESTS:-1}" = "1" ]; then
