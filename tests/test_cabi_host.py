@@ -124,6 +124,72 @@ def test_grouped_phase1_validation(dga, capfd):
     assert "[DGA] [ERROR]" in capfd.readouterr().err
 
 
+def test_round2_entry_points_validate_on_the_host(dga, capfd):
+    """The entries added in round 2 refuse what they do not serve BEFORE anything touches a device: the group
+    alignment promise, the two-GEMM decode launch, the matmul that allocates nothing."""
+    BF16, F16, I32 = 27, 1, 3
+    L = dga._lib.lib
+    INVALID, NULLPTR = 161002, 161001
+    # --- dgaSetExecutorGroupAlignment: 128 or 256, must divide the row count; only grouped executors
+    w = _desc(dga, (4, 512, 128), (512 * 128, 128, 1), BF16)
+
+    def grouped(rows):
+        ws, ex = ctypes.c_uint64(0), ctypes.c_void_p(None)
+        rc = L.dgaMGroupedMatmulGetWorkspaceSize(ctypes.byref(_desc(dga, (rows, 128), (128, 1), BF16)), ctypes.byref(w),
+                                                 ctypes.byref(_desc(dga, (rows,), (1,), I32)),
+                                                 ctypes.byref(_desc(dga, (rows, 512), (512, 1), BF16)),
+                                                 ctypes.byref(ws), ctypes.byref(ex))
+        assert rc == 0
+        return ex
+    ex = grouped(512)
+    assert L.dgaSetExecutorGroupAlignment(ex, 256) == 0
+    assert L.dgaSetExecutorGroupAlignment(ex, 128) == 0
+    assert L.dgaSetExecutorGroupAlignment(ex, 64) == INVALID
+    L.dgaDestroyExecutor(ex)
+    ex = grouped(384)
+    assert L.dgaSetExecutorGroupAlignment(ex, 256) == INVALID      # 384 rows are not whole pairs
+    L.dgaDestroyExecutor(ex)
+    assert L.dgaSetExecutorGroupAlignment(None, 256) == NULLPTR
+    ok = (_desc(dga, (64, 128), (128, 1), BF16), _desc(dga, (128, 256), (1, 128), BF16),
+          _desc(dga, (64, 256), (256, 1), BF16))
+    ws, ex = ctypes.c_uint64(0), ctypes.c_void_p(None)
+    assert L.aclnnCatlassDynamicMatmulGetWorkspaceSize(*[ctypes.byref(t) for t in ok], ctypes.byref(ws), ctypes.byref(ex)) == 0
+    assert L.dgaSetExecutorGroupAlignment(ex, 256) == NULLPTR      # a dense executor
+    L.dgaDestroyExecutor(ex)
+
+    # --- dgaDecodePairMatmul
+    def pair(self_t, w1, o1, w2, o2):
+        return L.dgaDecodePairMatmul(*[None if t is None else ctypes.byref(t) for t in (self_t, w1, o1, w2, o2)], None)
+    x = _desc(dga, (256, 128), (128, 1), BF16)
+    wa, oa = _desc(dga, (128, 256), (1, 128), BF16), _desc(dga, (256, 256), (256, 1), BF16)
+    assert pair(x, wa, oa, wa, oa) == INVALID                                      # m > 128
+    x64, o64 = _desc(dga, (64, 128), (128, 1), BF16), _desc(dga, (64, 256), (256, 1), BF16)
+    assert pair(x64, wa, o64, _desc(dga, (128, 256), (256, 1), BF16), o64) == INVALID   # row-major second weight
+    assert pair(x64, wa, o64, _desc(dga, (96, 256), (1, 96), BF16), o64) == INVALID     # K mismatch
+    assert pair(x64, wa, o64, wa, _desc(dga, (64, 256), (256, 1), 0)) == INVALID        # two output dtypes
+    x_odd = _desc(dga, (64, 100), (100, 1), BF16)                                       # 200-byte rows: no repack here
+    assert pair(x_odd, _desc(dga, (100, 256), (1, 100), BF16), o64, _desc(dga, (100, 256), (1, 100), BF16), o64) == INVALID
+    assert pair(None, wa, o64, wa, o64) == NULLPTR
+
+    # --- dgaSplitkMatmulNoAlloc: the size limit and the argument rules come before the first CUDA call
+    p = ctypes.c_void_p(0x10000)
+    limit = dga._lib.NO_ALLOC_SCRATCH_BYTES
+    header = open(os.path.join(ROOT, "include", "dga_b200.h")).read()
+    assert re.search(r"#define\s+DGA_NO_ALLOC_SCRATCH_BYTES\s+\(32u\s*<<\s*20\)", header) and limit == 32 << 20
+    capfd.readouterr()
+    assert L.dgaSplitkMatmulNoAlloc(p, p, p, 4096, 4096, 4096, BF16, BF16, 1, 4, None) == INVALID
+    err = capfd.readouterr().err
+    assert str(4 * 4096 * 4096 * 4) in err and str(limit) in err
+    assert L.dgaSplitkMatmulNoAlloc(p, p, p, 2048, 4096, 1024, BF16, BF16, 1, 0, None) == INVALID   # automatic split: 64 MiB
+    assert L.dgaSplitkMatmulNoAlloc(None, p, p, 256, 256, 256, BF16, BF16, 1, 2, None) == NULLPTR
+    assert L.dgaSplitkMatmulNoAlloc(p, p, p, 256, 256, 256, 0, 0, 1, 2, None) == INVALID            # fp32 inputs
+    assert L.dgaSplitkMatmulNoAlloc(p, p, p, 256, 256, 256, BF16, F16, 1, 2, None) == INVALID       # bf16 in, fp16 out
+    assert L.dgaSplitkMatmulNoAlloc(p, p, p, 256, 256, 256, BF16, BF16, 1, 17, None) == INVALID     # > 16 slices
+    assert L.dgaSplitkMatmulNoAlloc(p, p, p, 256, 256, 64, BF16, BF16, 1, 2, None) == INVALID       # one K block
+    assert L.dgaSplitkMatmulNoAlloc(p, p, p, 256, 256, 1001, BF16, BF16, 1, 2, None) != 0           # unaligned rows
+    assert L.dgaSplitkMatmulNoAlloc(p, p, p, 0, 256, 256, BF16, BF16, 1, 2, None) == INVALID        # empty
+
+
 SWEEP = [1, 16, 64, 128, 512, 2048, 8192]
 
 
