@@ -323,6 +323,17 @@ static int launch_common_out(const DenseLaunch& L, const GemmParams& gp, cudaStr
     return ACLNN_ERR_PARAM_INVALID;
 }
 
+// Columns per output store of the plain (whole-tile, 2-D output) launches.  $DGA_EPI_COLS=32 forces 64-byte store rows
+// where 128-byte rows would be used: a measurement aid for the peer stores of the N-sharded step, whose NVLink rate
+// follows the size of the write (config 5 on 8 GPUs: 3.98 ms with 64-byte rows, 2.61 ms with 128-byte rows; 256-byte
+// rows - two adjacent swizzle lines per row in one store box - change nothing, the store engine writes 128-byte
+// lines: profiles/r02_nshard_store_rows_g8.log).
+static uint32_t plain_epi_cols(uint32_t block_n, uint32_t out_elem_bytes) {
+    static const uint32_t forced = [] { const char* e = std::getenv("DGA_EPI_COLS"); return e ? uint32_t(std::atoi(e)) : 0u; }();
+    const uint32_t cols = epi_cols_for(block_n, out_elem_bytes);
+    return forced == 32 ? 32u : cols;
+}
+
 static int encode_common(DenseLaunch& L) {
     const DgaTilingPlan& p = L.plan;
     const uint32_t cta = p.ctaGroup, load_n = p.n1 / cta;
@@ -371,7 +382,7 @@ static int encode_common(DenseLaunch& L) {
     else  // row-major [K, N]: boxes of 64 columns x 64 k-rows
         rc = make_tmap_2d(&L.tm_b, L.eff.b, p.dtype, p.n, p.k, L.eff.ldb, 64, 64, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc != ACLNN_SUCCESS) return rc;
-    const uint32_t epi = epi_cols_for(p.n1, elem_bytes(p.outDtype));
+    const uint32_t epi = plain_epi_cols(p.n1, elem_bytes(p.outDtype));
     const bool wide = epi * elem_bytes(p.outDtype) == 128;
     const CUtensorMapSwizzle d_swz = wide ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
     for (uint32_t i = 0; i < L.num_peers; ++i) {
@@ -419,7 +430,7 @@ static void common_params(const DgaTilingPlan& p, GemmParams& gp) {
     gp.idesc = make_idesc(128 * cta, p.n1, p.dtype == ACL_BF16 ? 1u : 0u, 0, p.layoutTagB == 1 ? 0u : 1u);
     gp.b_stage_bytes = (p.n1 / cta) * 128;
     gp.k_block_elems = 64;
-    gp.epi_cols = epi_cols_for(p.n1, elem_bytes(p.outDtype));
+    gp.epi_cols = plain_epi_cols(p.n1, elem_bytes(p.outDtype));
     gp.dp_tiles = gp.num_m_blocks * gp.num_n_blocks;
     gp.sk_tiles = 0;
 }
